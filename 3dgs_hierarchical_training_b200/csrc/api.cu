@@ -1,0 +1,245 @@
+// extern "C" boundary of libhtgs.so (see include/htgs.h).  Host-side only:
+// carves the caller-owned work buffers, orders the kernel launches on the
+// caller's stream, reports errors through htgs_last_error().
+#include "../../include/htgs.h"
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace htgs {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+template <typename T>
+static T* carve(char*& p, size_t count) {
+    p = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256));
+    T* r = reinterpret_cast<T*>(p);
+    p += count * sizeof(T);
+    return r;
+}
+
+GeomView geom_view(void* base, int P) {
+    GeomView g;
+    char* p = reinterpret_cast<char*>(base);
+    const size_t n = (size_t)P;
+    const size_t nb = (n + HTGS_PRE_BLOCK - 1) / HTGS_PRE_BLOCK;
+    g.means2D = carve<float2>(p, n);
+    g.conic_opacity = carve<float4>(p, n);
+    g.feat = carve<float4>(p, n);
+    g.clamped = carve<uint8_t>(p, n);
+    g.tiles_touched = carve<uint32_t>(p, n);
+    g.point_offsets = carve<uint32_t>(p, n);
+    g.block_sums = carve<uint32_t>(p, nb + 1);
+    g.num_rendered = carve<uint32_t>(p, 4);
+    g.bytes = (size_t)(p - reinterpret_cast<char*>(base)) + 256;
+    return g;
+}
+
+BinView bin_view(void* base, int64_t R, int W, int H) {
+    (void)W; (void)H;
+    BinView b;
+    char* p = reinterpret_cast<char*>(base);
+    const size_t n = (size_t)(R > 0 ? R : 0);
+    b.keys_sorted = carve<uint64_t>(p, n);
+    b.values_sorted = carve<uint32_t>(p, n);
+    b.keys_alt = carve<uint64_t>(p, n);
+    b.values_alt = carve<uint32_t>(p, n);
+    b.sort_scratch = carve<char>(p, sort_scratch_bytes(R));
+    b.bytes = (size_t)(p - reinterpret_cast<char*>(base)) + 256;
+    return b;
+}
+
+ImgView img_view(void* base, int W, int H) {
+    ImgView v;
+    char* p = reinterpret_cast<char*>(base);
+    const size_t tiles = (size_t)((W + HTGS_TILE - 1) / HTGS_TILE) * ((H + HTGS_TILE - 1) / HTGS_TILE);
+    v.ranges = carve<uint2>(p, tiles);
+    v.n_contrib = carve<uint32_t>(p, (size_t)W * H);
+    v.bytes = (size_t)(p - reinterpret_cast<char*>(base)) + 256;
+    return v;
+}
+
+static bool aligned256(const void* p) { return (reinterpret_cast<size_t>(p) & 255) == 0; }
+
+}  // namespace htgs
+
+using namespace htgs;
+
+extern "C" {
+
+int htgs_abi_version(void) { return HTGS_ABI_VERSION; }
+const char* htgs_last_error(void) { return g_error; }
+
+size_t htgs_geom_bytes(int P) { return geom_view(nullptr, P < 0 ? 0 : P).bytes; }
+size_t htgs_image_bytes(int W, int H) { return img_view(nullptr, W, H).bytes; }
+size_t htgs_binning_bytes(int64_t R, int W, int H) { return bin_view(nullptr, R, W, H).bytes; }
+size_t htgs_backward_scratch_bytes(int P) { return align_up((size_t)(P < 0 ? 0 : P) * 12 * sizeof(float), 256) + 256; }
+size_t htgs_sort_scratch_bytes(int64_t n) { return sort_scratch_bytes(n); }
+
+int htgs_geom_layout(int P, size_t* offsets, int cap) {
+    GeomView g = geom_view(nullptr, P);
+    const size_t o[HTGS_GEOM_NFIELDS] = {(size_t)g.means2D, (size_t)g.conic_opacity, (size_t)g.feat, (size_t)g.clamped,
+                                         (size_t)g.tiles_touched, (size_t)g.point_offsets, (size_t)g.block_sums,
+                                         (size_t)g.num_rendered};
+    int k = 0;
+    for (; k < HTGS_GEOM_NFIELDS && k < cap; k++) offsets[k] = o[k];
+    return k;
+}
+int htgs_binning_layout(int64_t R, int W, int H, size_t* offsets, int cap) {
+    BinView b = bin_view(nullptr, R, W, H);
+    const size_t o[HTGS_BIN_NFIELDS] = {(size_t)b.keys_sorted, (size_t)b.values_sorted, (size_t)b.keys_alt,
+                                        (size_t)b.values_alt, (size_t)b.sort_scratch};
+    int k = 0;
+    for (; k < HTGS_BIN_NFIELDS && k < cap; k++) offsets[k] = o[k];
+    return k;
+}
+int htgs_image_layout(int W, int H, size_t* offsets, int cap) {
+    ImgView v = img_view(nullptr, W, H);
+    const size_t o[HTGS_IMG_NFIELDS] = {(size_t)v.ranges, (size_t)v.n_contrib};
+    int k = 0;
+    for (; k < HTGS_IMG_NFIELDS && k < cap; k++) offsets[k] = o[k];
+    return k;
+}
+
+int htgs_forward_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
+                            const float* rotations, const float* opacities, const float* shs,
+                            const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                            const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                            int prefiltered, void* geom_buf, int* radii, int64_t* num_rendered_host, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (num_rendered_host) *num_rendered_host = 0;
+    if (P < 0 || W <= 0 || H <= 0) { set_error("htgs_forward_preprocess: bad sizes P=%d W=%d H=%d", P, W, H); return 1; }
+    if (P == 0) return 0;
+    if (!means3D || !opacities || !viewmatrix || !projmatrix || !campos || !geom_buf || !radii || !num_rendered_host) {
+        set_error("htgs_forward_preprocess: null required pointer");
+        return 1;
+    }
+    if (!shs && !colors_precomp) {
+        // reference: "For non-RGB, provide precomputed Gaussian colors!" is the closest it gets; the plugin
+        // layer raises before reaching here (diff_gaussian_rasterization/__init__.py:194-195)
+        set_error("htgs_forward_preprocess: need shs or colors_precomp");
+        return 1;
+    }
+    if (!cov3D_precomp && (!scales || !rotations)) { set_error("htgs_forward_preprocess: need scales+rotations or cov3D_precomp"); return 1; }
+    if (D < 0 || D > 3) { set_error("htgs_forward_preprocess: sh degree %d outside 0..3", D); return 1; }
+    if (shs && !colors_precomp && M < (D + 1) * (D + 1)) { set_error("htgs_forward_preprocess: M=%d too small for degree %d", M, D); return 1; }
+    if (!aligned256(geom_buf)) { set_error("htgs_forward_preprocess: geom_buf must be 256-byte aligned"); return 1; }
+    if (rotations && (reinterpret_cast<size_t>(rotations) & 15)) { set_error("htgs_forward_preprocess: rotations must be 16-byte aligned"); return 1; }
+    GeomView g = geom_view(geom_buf, P);
+    if (launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+                          viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, g, radii, st)) return 1;
+    if (launch_scan_block_sums(P, g, st)) return 1;
+    uint32_t r32 = 0;
+    HTGS_CUDA_CHECK(cudaMemcpyAsync(&r32, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    HTGS_CUDA_CHECK(cudaStreamSynchronize(st));
+    *num_rendered_host = (int64_t)r32;
+    return 0;
+}
+
+int htgs_forward_render(int P, int64_t R, int W, int H, const float* background, const int* radii, void* geom_buf,
+                        void* binning_buf, void* image_buf, float* out_color, float* out_depth, float* out_alpha,
+                        void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (P <= 0) return 0;
+    if (!background || !radii || !geom_buf || !image_buf || !out_color || !out_depth || !out_alpha || (R > 0 && !binning_buf)) {
+        set_error("htgs_forward_render: null required pointer");
+        return 1;
+    }
+    if (!aligned256(geom_buf) || !aligned256(image_buf) || (R > 0 && !aligned256(binning_buf))) {
+        set_error("htgs_forward_render: work buffers must be 256-byte aligned");
+        return 1;
+    }
+    if (R < 0 || R >= (int64_t(1) << 30)) { set_error("htgs_forward_render: R=%lld out of range", (long long)R); return 1; }
+    GeomView g = geom_view(geom_buf, P);
+    ImgView img = img_view(image_buf, W, H);
+    BinView b = bin_view(binning_buf, R, W, H);
+    const int gx = (W + HTGS_TILE - 1) / HTGS_TILE, gy = (H + HTGS_TILE - 1) / HTGS_TILE;
+    if (R > 0) {
+        const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));  // rasterizer_impl.cu:301-309
+        const int passes = sort_num_passes(end_bit);
+        // start in the buffer that makes the last pass land in keys_sorted/values_sorted
+        uint64_t* k0 = (passes & 1) ? b.keys_alt : b.keys_sorted;
+        uint32_t* v0 = (passes & 1) ? b.values_alt : b.values_sorted;
+        uint64_t* k1 = (passes & 1) ? b.keys_sorted : b.keys_alt;
+        uint32_t* v1 = (passes & 1) ? b.values_sorted : b.values_alt;
+        if (launch_make_keys(P, W, H, radii, g, k0, v0, st)) return 1;
+        if (sort_pairs(R, end_bit, k0, v0, k1, v1, b.sort_scratch, st)) return 1;
+    }
+    if (launch_tile_ranges(R, W, H, b.keys_sorted, img.ranges, st)) return 1;
+    if (launch_blend_forward(W, H, img.ranges, b.values_sorted, g, background, out_color, out_depth, out_alpha,
+                             img.n_contrib, st)) return 1;
+    return 0;
+}
+
+int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
+                  const float* shs, const float* colors_precomp, const float* alphas, const float* scales,
+                  float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                  const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int* radii,
+                  const void* geom_buf, const void* binning_buf, const void* image_buf, const float* dL_dout_color,
+                  const float* dL_dout_depth, const float* dL_dout_alpha, void* scratch, float* dL_dmeans2D,
+                  float* dL_dopacity, float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                  float* dL_dscales, float* dL_drotations, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (P <= 0) return 0;
+    if (!background || !means3D || !alphas || !viewmatrix || !projmatrix || !campos || !radii || !geom_buf || !image_buf ||
+        !dL_dout_color || !dL_dout_depth || !dL_dout_alpha || !scratch || !dL_dmeans2D || !dL_dopacity || !dL_dmeans3D ||
+        (R > 0 && !binning_buf)) {
+        set_error("htgs_backward: null required pointer");
+        return 1;
+    }
+    if (shs && !dL_dsh) { set_error("htgs_backward: dL_dsh required with shs"); return 1; }
+    if (colors_precomp && !dL_dcolors) { set_error("htgs_backward: dL_dcolors required with colors_precomp"); return 1; }
+    if (scales && (!rotations || !dL_dscales || !dL_drotations)) { set_error("htgs_backward: scale/rotation outputs required"); return 1; }
+    if (!scales && !cov3D_precomp) { set_error("htgs_backward: need scales+rotations or cov3D_precomp"); return 1; }
+    if (cov3D_precomp && !dL_dcov3D) { set_error("htgs_backward: dL_dcov3D required with cov3D_precomp"); return 1; }
+    if (!aligned256(scratch) || !aligned256(geom_buf) || !aligned256(image_buf)) { set_error("htgs_backward: buffers must be 256-byte aligned"); return 1; }
+    if ((dL_drotations && (reinterpret_cast<size_t>(dL_drotations) & 15)) || (rotations && (reinterpret_cast<size_t>(rotations) & 15))) {
+        set_error("htgs_backward: rotations / dL_drotations must be 16-byte aligned");
+        return 1;
+    }
+    GeomView g = geom_view(const_cast<void*>(geom_buf), P);
+    ImgView img = img_view(const_cast<void*>(image_buf), W, H);
+    BinView b = bin_view(const_cast<void*>(binning_buf), R, W, H);
+    float* gacc = reinterpret_cast<float*>(scratch);
+    HTGS_CUDA_CHECK(cudaMemsetAsync(gacc, 0, (size_t)P * 12 * sizeof(float), st));
+    if (R > 0) {
+        if (launch_blend_backward(P, W, H, img.ranges, b.values_sorted, g, background, alphas, img.n_contrib, dL_dout_color,
+                                  dL_dout_depth, dL_dout_alpha, gacc, st)) return 1;
+    }
+    // the SH path feeds dL/dcolour into dL/dsh; only the precomputed-colour path returns it
+    if (launch_geom_backward(P, D, M, means3D, radii, shs, colors_precomp, scales, scale_modifier, rotations, cov3D_precomp,
+                             viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, g, gacc, dL_dmeans2D, dL_dopacity,
+                             dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, st)) return 1;
+    return 0;
+}
+
+int htgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                      void* stream) {
+    (void)projmatrix;
+    if (P <= 0) return 0;
+    if (!means3D || !viewmatrix || !present) { set_error("htgs_mark_visible: null pointer"); return 1; }
+    return launch_mark_visible(P, means3D, viewmatrix, present, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int htgs_sort_pairs(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* values_in, uint64_t* keys_out,
+                    uint32_t* values_out, void* scratch, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (n <= 0) return 0;
+    if (!keys_in || !values_in || !keys_out || !values_out || !scratch) { set_error("htgs_sort_pairs: null pointer"); return 1; }
+    if (sort_pairs(n, end_bit, keys_in, values_in, keys_out, values_out, scratch, st)) return 1;
+    if ((sort_num_passes(end_bit) & 1) == 0) {  // even pass count: result sits in the input buffers
+        HTGS_CUDA_CHECK(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+        HTGS_CUDA_CHECK(cudaMemcpyAsync(values_out, values_in, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,108 @@
+// K4: front-to-back alpha blend of one 16x16 tile per CTA.
+// Replaces FORWARD::render / renderCUDA (cuda_rasterizer/forward.cu:261-381).
+//
+// Bound: FP32 issue (about 20 FP32-pipe instructions + 1 MUFU per tested
+// pixel/Gaussian pair); the lever is testing fewer pairs.  Gaussians are staged
+// in shared memory in batches of 256 together with colour+depth (the reference
+// re-fetches those from global memory per blended pair, forward.cu:359-361) and
+// an 8-bit reach mask (blend_common.cuh); each warp walks only the Gaussians
+// that can reach its 8x4 pixel block and leaves as soon as its 32 pixels are
+// saturated.  Per-pixel arithmetic is the reference's, operation for operation,
+// so colour/depth/alpha/n_contrib are bit-identical.
+#include "blend_common.cuh"
+
+namespace htgs {
+
+constexpr int FWD_BATCH = 256;
+
+__global__ void __launch_bounds__(HTGS_TILE_PIX)
+blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                     const float4* __restrict__ feat, const float* __restrict__ bg, float* __restrict__ out_color,
+                     float* __restrict__ out_depth, float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib) {
+    __shared__ float4 s_co[FWD_BATCH];
+    __shared__ float4 s_feat[FWD_BATCH];
+    __shared__ float2 s_xy[FWD_BATCH];
+    __shared__ uint8_t s_mask[FWD_BATCH];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile_x0 = blockIdx.x * HTGS_TILE, tile_y0 = blockIdx.y * HTGS_TILE;
+    const int px = tile_x0 + warp_block_x(warp) + (lane & 7);
+    const int py = tile_y0 + warp_block_y(warp) + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    bool done = !inside;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int n = (int)(range.y - range.x);
+
+    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, dsum = 0.f;
+    uint32_t last_contributor = 0;
+
+    for (int base = 0; base < n; base += FWD_BATCH) {
+        // leave when every pixel of the tile is saturated (forward.cu:313-315)
+        if (__syncthreads_count(done) == HTGS_TILE_PIX) break;
+        const int cnt = min(FWD_BATCH, n - base);
+        if (tid < cnt) {
+            const uint32_t g = point_list[range.x + base + tid];
+            const float2 xy = means2D[g];
+            const float4 co = conic_opacity[g];
+            s_xy[tid] = xy;
+            s_co[tid] = co;
+            s_feat[tid] = feat[g];
+            s_mask[tid] = (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
+        }
+        __syncthreads();
+        if (__all_sync(0xffffffffu, done)) continue;
+        for (int c0 = 0; c0 < cnt; c0 += 32) {
+            const int j = c0 + lane;
+            const bool mine = j < cnt && ((s_mask[j] >> warp) & 1);
+            uint32_t m = __ballot_sync(0xffffffffu, mine);
+            while (m) {
+                const int idx = c0 + __ffs(m) - 1;
+                m &= m - 1;
+                if (done) continue;
+                const float2 xy = s_xy[idx];
+                const float4 co = s_co[idx];
+                const float dx = SB(xy.x, pxf), dy = SB(xy.y, pyf);
+                const float power = pair_power(dx, dy, co.x, co.y, co.z);
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, MU(co.w, expf(power)));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = MU(T, SB(1.0f, alpha));
+                if (test_T < 0.0001f) { done = true; continue; }
+                const float4 f = s_feat[idx];
+                C0 = FM(T, MU(alpha, f.x), C0);
+                C1 = FM(T, MU(alpha, f.y), C1);
+                C2 = FM(T, MU(alpha, f.z), C2);
+                wsum = FM(T, alpha, wsum);
+                dsum = FM(T, MU(alpha, f.w), dsum);
+                T = test_T;
+                last_contributor = (uint32_t)(base + idx + 1);
+            }
+            if (__all_sync(0xffffffffu, done)) break;
+        }
+    }
+    if (inside) {
+        const size_t pix = (size_t)py * W + px;
+        const size_t plane = (size_t)H * W;
+        n_contrib[pix] = last_contributor;
+        out_color[pix] = FM(T, bg[0], C0);
+        out_color[plane + pix] = FM(T, bg[1], C1);
+        out_color[2 * plane + pix] = FM(T, bg[2], C2);
+        out_alpha[pix] = wsum;  // forward.cu:378: the accumulated weight, not 1-T
+        out_depth[pix] = dsum;
+    }
+}
+
+int launch_blend_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                         const float* bg, float* out_color, float* out_depth, float* out_alpha,
+                         uint32_t* n_contrib, cudaStream_t st) {
+    const dim3 grid((W + HTGS_TILE - 1) / HTGS_TILE, (H + HTGS_TILE - 1) / HTGS_TILE);
+    blend_forward_kernel<<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, g.means2D, g.conic_opacity, g.feat, bg,
+                                                         out_color, out_depth, out_alpha, n_contrib);
+    HTGS_LAUNCH_CHECK("blend_forward_kernel");
+    return 0;
+}
+
+}  // namespace htgs

@@ -1,0 +1,303 @@
+// K6 + K7 fused: per-Gaussian backward of the projection.
+// Replaces computeCov2DCUDA and BACKWARD::preprocessCUDA
+// (cuda_rasterizer/backward.cu:144-274, :346-412, SH backward :20-139,
+// scale/rotation backward :278-341) and the ten zero-filled gradient tensors of
+// rasterize_points.cu:158-167.
+//
+// HBM-bound streaming kernel, one thread per Gaussian: reads the 48 B
+// accumulator row written by the blend backward plus the Gaussian's parameters,
+// recomputes cov3D / T instead of loading stored copies, and writes EVERY output
+// element exactly once (zeros for culled Gaussians), so the caller allocates the
+// outputs uninitialised and no memset pass over 300 B/Gaussian is needed.
+#include "gs_math.cuh"
+
+namespace htgs {
+
+__device__ __forceinline__ void store3(float* p, float a, float b, float c) { p[0] = a; p[1] = b; p[2] = c; }
+
+template <bool VEC>
+__device__ __forceinline__ void write_sh_grad(float* __restrict__ out, const float* w, int ncoef_active, int M,
+                                              float g0, float g1, float g2) {
+    // out[k*3 + c] = w[k] * g[c] for k < ncoef_active, 0 above
+    const int total = M * 3;
+    if (VEC) {
+        float4* o4 = reinterpret_cast<float4*>(out);
+        for (int i = 0; i < total / 4; i++) {
+            float r[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int e = 4 * i + t, k = e / 3, c = e - 3 * k;
+                const float g = c == 0 ? g0 : (c == 1 ? g1 : g2);
+                r[t] = k < ncoef_active ? w[k] * g : 0.f;
+            }
+            o4[i] = make_float4(r[0], r[1], r[2], r[3]);
+        }
+    } else {
+        for (int e = 0; e < total; e++) {
+            const int k = e / 3, c = e - 3 * k;
+            const float g = c == 0 ? g0 : (c == 1 ? g1 : g2);
+            out[e] = k < ncoef_active ? w[k] * g : 0.f;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                     const float* __restrict__ shs, const uint8_t* __restrict__ clamped, bool colors_are_precomp,
+                     const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
+                     const float* __restrict__ cov3D_precomp, const float* __restrict__ viewmatrix,
+                     const float* __restrict__ projmatrix, const float* __restrict__ campos, float h_x, float h_y,
+                     float tanfovx, float tanfovy, const float* __restrict__ gacc, float* __restrict__ dL_dmeans2D,
+                     float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors, float* __restrict__ dL_dmeans3D,
+                     float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
+                     float* __restrict__ dL_drotations) {
+    __shared__ float s_cam[35];
+    if (threadIdx.x < 16) s_cam[threadIdx.x] = viewmatrix[threadIdx.x];
+    else if (threadIdx.x < 32) s_cam[threadIdx.x] = projmatrix[threadIdx.x - 16];
+    else if (threadIdx.x < 35) s_cam[threadIdx.x] = campos[threadIdx.x - 32];
+    __syncthreads();
+    const float* vm = s_cam;
+    const float* proj = s_cam + 16;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const bool sh_vec = dL_dsh != nullptr && ((M * 3) % 4 == 0) && ((reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0);
+
+    if (!(radii[idx] > 0)) {
+        store3(dL_dmeans2D + 3 * (size_t)idx, 0.f, 0.f, 0.f);
+        dL_dopacity[idx] = 0.f;
+        store3(dL_dmeans3D + 3 * (size_t)idx, 0.f, 0.f, 0.f);
+        if (dL_dcolors) store3(dL_dcolors + 3 * (size_t)idx, 0.f, 0.f, 0.f);
+        if (dL_dcov3D) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = 0.f;
+        }
+        if (dL_dsh) {
+            float* o = dL_dsh + (size_t)idx * M * 3;
+            if (sh_vec) {
+                for (int i = 0; i < M * 3 / 4; i++) reinterpret_cast<float4*>(o)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+                for (int i = 0; i < M * 3; i++) o[i] = 0.f;
+            }
+        }
+        if (dL_dscales) store3(dL_dscales + 3 * (size_t)idx, 0.f, 0.f, 0.f);
+        if (dL_drotations) reinterpret_cast<float4*>(dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        return;
+    }
+
+    const float4* ga = reinterpret_cast<const float4*>(gacc + (size_t)idx * 12);
+    const float4 g0 = ga[0], g1 = ga[1], g2 = ga[2];
+    const float g2x = g0.x, g2y = g0.y, g_opacity = g0.z, g_depth = g0.w;
+    const float dcx = g1.x, dcy = g1.y, dcz = g1.z;  // dL/dconic .x .y .w  (backward.cu:165)
+    const float gc0 = g2.x, gc1 = g2.y, gc2 = g2.z;  // dL/dcolour
+
+    const float mx = means3D[3 * (size_t)idx], my = means3D[3 * (size_t)idx + 1], mz = means3D[3 * (size_t)idx + 2];
+
+    // ---- covariance: recompute what the forward used ----
+    float c3[6];
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * (size_t)idx + k];
+    } else {
+        q = reinterpret_cast<const float4*>(rotations)[idx];
+        sc0 = scales[3 * (size_t)idx]; sc1 = scales[3 * (size_t)idx + 1]; sc2 = scales[3 * (size_t)idx + 2];
+        cov3d_from_scale_rot(sc0, sc1, sc2, scale_modifier, q, c3);
+    }
+
+    // ---- computeCov2DCUDA, backward.cu:144-274 ----
+    const Ewa e = ewa_setup(mx, my, mz, vm, h_x, h_y, tanfovx, tanfovy);
+    const float x_grad_mul = (e.txtz < -e.limx || e.txtz > e.limx) ? 0.f : 1.f;
+    const float y_grad_mul = (e.tytz < -e.limy || e.tytz > e.limy) ? 0.f : 1.f;
+    float a, b, c;
+    ewa_cov2d(e, c3, a, b, c);
+    const float denom = a * c - b * b;
+    float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    const float T00 = e.T00, T01 = e.T01, T02 = e.T02, T10 = e.T10, T11 = e.T11, T12 = e.T12;
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (denom2inv != 0.f) {
+        dL_da = denom2inv * (-c * c * dcx + 2 * b * c * dcy + (denom - a * c) * dcz);
+        dL_dc = denom2inv * (-a * a * dcz + 2 * a * b * dcy + (denom - a * c) * dcx);
+        dL_db = denom2inv * 2 * (b * c * dcx - (denom + 2 * b * b) * dcy + a * b * dcz);
+        dcov[0] = (T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc);
+        dcov[3] = (T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc);
+        dcov[5] = (T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc);
+        dcov[1] = 2 * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2 * T10 * T11 * dL_dc;
+        dcov[2] = 2 * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2 * T10 * T12 * dL_dc;
+        dcov[4] = 2 * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2 * T11 * T12 * dL_dc;
+    }
+    // rows of Vrk * T[0] and Vrk * T[1]
+    const float vt0x = T00 * c3[0] + T01 * c3[1] + T02 * c3[2];
+    const float vt0y = T00 * c3[1] + T01 * c3[3] + T02 * c3[4];
+    const float vt0z = T00 * c3[2] + T01 * c3[4] + T02 * c3[5];
+    const float vt1x = T10 * c3[0] + T11 * c3[1] + T12 * c3[2];
+    const float vt1y = T10 * c3[1] + T11 * c3[3] + T12 * c3[4];
+    const float vt1z = T10 * c3[2] + T11 * c3[4] + T12 * c3[5];
+    const float dL_dT00 = 2 * vt0x * dL_da + vt1x * dL_db;
+    const float dL_dT01 = 2 * vt0y * dL_da + vt1y * dL_db;
+    const float dL_dT02 = 2 * vt0z * dL_da + vt1z * dL_db;
+    const float dL_dT10 = 2 * vt1x * dL_dc + vt0x * dL_db;
+    const float dL_dT11 = 2 * vt1y * dL_dc + vt0y * dL_db;
+    const float dL_dT12 = 2 * vt1z * dL_dc + vt0z * dL_db;
+    const float dL_dJ00 = vm[0] * dL_dT00 + vm[4] * dL_dT01 + vm[8] * dL_dT02;
+    const float dL_dJ02 = vm[2] * dL_dT00 + vm[6] * dL_dT01 + vm[10] * dL_dT02;
+    const float dL_dJ11 = vm[1] * dL_dT10 + vm[5] * dL_dT11 + vm[9] * dL_dT12;
+    const float dL_dJ12 = vm[2] * dL_dT10 + vm[6] * dL_dT11 + vm[10] * dL_dT12;
+    const float tz = 1.f / e.tz, tz2 = tz * tz, tz3 = tz2 * tz;
+    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * e.tx) * tz3 * dL_dJ02 +
+                         (2 * h_y * e.ty) * tz3 * dL_dJ12;
+    float dmx = vm[0] * dL_dtx + vm[1] * dL_dty + vm[2] * dL_dtz;  // backward.cu:268-273
+    float dmy = vm[4] * dL_dtx + vm[5] * dL_dty + vm[6] * dL_dtz;
+    float dmz = vm[8] * dL_dtx + vm[9] * dL_dty + vm[10] * dL_dtz;
+
+    // ---- preprocessCUDA backward, backward.cu:372-403 ----
+    const float m_hw = proj[3] * mx + proj[7] * my + proj[11] * mz + proj[15];
+    const float m_w = 1.0f / (m_hw + 0.0000001f);
+    const float mul1 = (proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12]) * m_w * m_w;
+    const float mul2 = (proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13]) * m_w * m_w;
+    dmx += (proj[0] * m_w - proj[3] * mul1) * g2x + (proj[1] * m_w - proj[3] * mul2) * g2y;
+    dmy += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
+    dmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
+    const float mul3 = vm[2] * mx + vm[6] * my + vm[10] * mz + vm[14];
+    dmx += (vm[2] - vm[3] * mul3) * g_depth;
+    dmy += (vm[6] - vm[7] * mul3) * g_depth;
+    dmz += (vm[10] - vm[11] * mul3) * g_depth;
+
+    // ---- SH backward, backward.cu:20-139 ----
+    if (shs != nullptr) {
+        const float ox = mx - s_cam[32], oy = my - s_cam[33], oz = mz - s_cam[34];
+        const float len = sqrtf(ox * ox + oy * oy + oz * oz);
+        const float x = ox / len, y = oy / len, z = oz / len;
+        const uint32_t cl = clamped[idx];
+        const float r0 = (cl & 1) ? 0.f : gc0, r1 = (cl & 2) ? 0.f : gc1, r2 = (cl & 4) ? 0.f : gc2;
+        const float* sh = shs + (size_t)idx * M * 3;
+        float w[16];
+        float ddx = 0.f, ddy = 0.f, ddz = 0.f;  // dL/ddir
+#define SHDOT(k) (sh[3 * (k)] * r0 + sh[3 * (k) + 1] * r1 + sh[3 * (k) + 2] * r2)
+        w[0] = HTGS_SH_C0;
+        int ncoef = 1;
+        if (D > 0) {
+            ncoef = 4;
+            w[1] = -HTGS_SH_C1 * y; w[2] = HTGS_SH_C1 * z; w[3] = -HTGS_SH_C1 * x;
+            ddx = -HTGS_SH_C1 * SHDOT(3);
+            ddy = -HTGS_SH_C1 * SHDOT(1);
+            ddz = HTGS_SH_C1 * SHDOT(2);
+            if (D > 1) {
+                ncoef = 9;
+                const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                w[4] = HTGS_SH_C2_0 * xy; w[5] = HTGS_SH_C2_1 * yz; w[6] = HTGS_SH_C2_2 * (2.f * zz - xx - yy);
+                w[7] = HTGS_SH_C2_3 * xz; w[8] = HTGS_SH_C2_4 * (xx - yy);
+                const float s4 = SHDOT(4), s5 = SHDOT(5), s6 = SHDOT(6), s7 = SHDOT(7), s8 = SHDOT(8);
+                ddx += HTGS_SH_C2_0 * y * s4 + HTGS_SH_C2_2 * 2.f * -x * s6 + HTGS_SH_C2_3 * z * s7 + HTGS_SH_C2_4 * 2.f * x * s8;
+                ddy += HTGS_SH_C2_0 * x * s4 + HTGS_SH_C2_1 * z * s5 + HTGS_SH_C2_2 * 2.f * -y * s6 + HTGS_SH_C2_4 * 2.f * -y * s8;
+                ddz += HTGS_SH_C2_1 * y * s5 + HTGS_SH_C2_2 * 2.f * 2.f * z * s6 + HTGS_SH_C2_3 * x * s7;
+                if (D > 2) {
+                    ncoef = 16;
+                    w[9] = HTGS_SH_C3_0 * y * (3.f * xx - yy);
+                    w[10] = HTGS_SH_C3_1 * xy * z;
+                    w[11] = HTGS_SH_C3_2 * y * (4.f * zz - xx - yy);
+                    w[12] = HTGS_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                    w[13] = HTGS_SH_C3_4 * x * (4.f * zz - xx - yy);
+                    w[14] = HTGS_SH_C3_5 * z * (xx - yy);
+                    w[15] = HTGS_SH_C3_6 * x * (xx - 3.f * yy);
+                    const float s9 = SHDOT(9), s10 = SHDOT(10), s11 = SHDOT(11), s12 = SHDOT(12), s13 = SHDOT(13),
+                                s14 = SHDOT(14), s15 = SHDOT(15);
+                    ddx += HTGS_SH_C3_0 * s9 * 3.f * 2.f * xy + HTGS_SH_C3_1 * s10 * yz + HTGS_SH_C3_2 * s11 * -2.f * xy +
+                           HTGS_SH_C3_3 * s12 * -3.f * 2.f * xz + HTGS_SH_C3_4 * s13 * (-3.f * xx + 4.f * zz - yy) +
+                           HTGS_SH_C3_5 * s14 * 2.f * xz + HTGS_SH_C3_6 * s15 * 3.f * (xx - yy);
+                    ddy += HTGS_SH_C3_0 * s9 * 3.f * (xx - yy) + HTGS_SH_C3_1 * s10 * xz +
+                           HTGS_SH_C3_2 * s11 * (-3.f * yy + 4.f * zz - xx) + HTGS_SH_C3_3 * s12 * -3.f * 2.f * yz +
+                           HTGS_SH_C3_4 * s13 * -2.f * xy + HTGS_SH_C3_5 * s14 * -2.f * yz +
+                           HTGS_SH_C3_6 * s15 * -3.f * 2.f * xy;
+                    ddz += HTGS_SH_C3_1 * s10 * xy + HTGS_SH_C3_2 * s11 * 4.f * 2.f * yz +
+                           HTGS_SH_C3_3 * s12 * 3.f * (2.f * zz - xx - yy) + HTGS_SH_C3_4 * s13 * 4.f * 2.f * xz +
+                           HTGS_SH_C3_5 * s14 * (xx - yy);
+                }
+            }
+        }
+#undef SHDOT
+        float* o = dL_dsh + (size_t)idx * M * 3;
+        if (sh_vec) write_sh_grad<true>(o, w, ncoef, M, r0, r1, r2);
+        else write_sh_grad<false>(o, w, ncoef, M, r0, r1, r2);
+        // dnormvdv, auxiliary.h:107-117
+        const float sum2 = ox * ox + oy * oy + oz * oz;
+        const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+        dmx += ((+sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * invsum32;
+        dmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
+        dmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
+    }
+
+    // ---- scale / rotation backward, backward.cu:278-341 ----
+    if (scales != nullptr) {
+        const float r = q.x, x = q.y, y = q.z, z = q.w;
+        // R[c][i]: glm column c, row i
+        const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                               {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                               {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+        const float s[3] = {scale_modifier * sc0, scale_modifier * sc1, scale_modifier * sc2};
+        const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                                {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                                {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+        float dMt[3][3];  // dL_dMt[c][i] = dL_dM[i][c],  dL_dM = 2*M*dL_dSigma, M[c][i] = s[i]*R[c][i]
+#pragma unroll
+        for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                float acc = 0.f;
+#pragma unroll
+                for (int k = 0; k < 3; k++) acc += (2.0f * s[i] * R[k][i]) * dS[cc][k];
+                dMt[i][cc] = acc;
+            }
+        float dsc[3];
+#pragma unroll
+        for (int cc = 0; cc < 3; cc++) dsc[cc] = R[0][cc] * dMt[cc][0] + R[1][cc] * dMt[cc][1] + R[2][cc] * dMt[cc][2];
+#pragma unroll
+        for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+            for (int i = 0; i < 3; i++) dMt[cc][i] *= s[cc];
+        float4 dq;
+        dq.x = 2 * z * (dMt[0][1] - dMt[1][0]) + 2 * y * (dMt[2][0] - dMt[0][2]) + 2 * x * (dMt[1][2] - dMt[2][1]);
+        dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) -
+               4 * x * (dMt[2][2] + dMt[1][1]);
+        dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) -
+               4 * y * (dMt[2][2] + dMt[0][0]);
+        dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) -
+               4 * z * (dMt[1][1] + dMt[0][0]);
+        store3(dL_dscales + 3 * (size_t)idx, dsc[0], dsc[1], dsc[2]);
+        reinterpret_cast<float4*>(dL_drotations)[idx] = dq;
+    }
+
+    store3(dL_dmeans2D + 3 * (size_t)idx, g2x, g2y, 0.f);
+    dL_dopacity[idx] = g_opacity;
+    store3(dL_dmeans3D + 3 * (size_t)idx, dmx, dmy, dmz);
+    if (dL_dcolors) {
+        if (colors_are_precomp) store3(dL_dcolors + 3 * (size_t)idx, gc0, gc1, gc2);
+        else store3(dL_dcolors + 3 * (size_t)idx, gc0, gc1, gc2);
+    }
+    if (dL_dcov3D) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+    }
+}
+
+int launch_geom_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
+                         const float* colors_precomp, const float* scales, float scale_modifier,
+                         const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                         const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                         const GeomView& g, const float* gacc, float* dL_dmeans2D, float* dL_dopacity,
+                         float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                         float* dL_drotations, cudaStream_t st) {
+    const float h_y = H / (2.0f * tanfovy), h_x = W / (2.0f * tanfovx);  // rasterizer_impl.cu:387-388
+    geom_backward_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, D, M, means3D, radii, shs, g.clamped, colors_precomp != nullptr,
+                                                          scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
+                                                          projmatrix, campos, h_x, h_y, tanfovx, tanfovy, gacc,
+                                                          dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D,
+                                                          dL_dsh, dL_dscales, dL_drotations);
+    HTGS_LAUNCH_CHECK("geom_backward_kernel");
+    return 0;
+}
+
+}  // namespace htgs

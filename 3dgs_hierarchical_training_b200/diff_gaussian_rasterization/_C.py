@@ -1,0 +1,158 @@
+"""Stand-in for the reference's pybind11 module `diff_gaussian_rasterization._C`
+(submodules/diff-gaussian-rasterization/ext.cpp:15-19, rasterize_points.cu).
+
+Same three entry points, same argument order, same returned tuples -- but the
+work is done by libhtgs.so through the C ABI of include/htgs.h; this file only
+allocates torch tensors and marshals raw pointers.  No fallback path exists:
+CPU tensors or a missing library raise.
+"""
+import ctypes
+
+import torch
+
+import htgs_native as nat
+
+NUM_CHANNELS = 3  # cuda_rasterizer/config.h:15
+
+
+def _f32c(t):
+    """What `.contiguous().data<float>()` does in rasterize_points.cu:96-115."""
+    if t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"expected scalar type Float but found {t.dtype}")
+    return t.contiguous()
+
+
+def _require_cuda(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: this rasterizer has no CPU path")
+
+
+def _stream(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug):
+    """RasterizeGaussiansCUDA (rasterize_points.cu:35-119).
+
+    Returns (num_rendered, out_color[3,H,W], out_depth[1,H,W], out_alpha[1,H,W], radii[P] int32,
+    geomBuffer, binningBuffer, imgBuffer) with the three buffers as opaque uint8 tensors."""
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    _require_cuda(means3D, "means3D")
+    dev = means3D.device
+    P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
+    f32 = dict(dtype=torch.float32, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    if P == 0:
+        # rasterize_points.cu:83: nothing is launched; images stay zero (background is NOT applied)
+        return (0, torch.zeros((NUM_CHANNELS, H, W), **f32), torch.zeros((1, H, W), **f32), torch.zeros((1, H, W), **f32),
+                torch.zeros((0,), dtype=torch.int32, device=dev), torch.empty(0, **u8), torch.empty(0, **u8),
+                torch.empty(0, **u8))
+    M = int(sh.size(1)) if sh.numel() != 0 and sh.size(0) != 0 else 0
+    means3D, colors, opacity, scales, rotations, cov3D_precomp, sh = map(
+        _f32c, (means3D, colors, opacity, scales, rotations, cov3D_precomp, sh))
+    background, viewmatrix, projmatrix, campos = map(_f32c, (background, viewmatrix, projmatrix, campos))
+    lib = nat.lib()
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        out_color = torch.empty((NUM_CHANNELS, H, W), **f32)
+        out_depth = torch.empty((1, H, W), **f32)
+        out_alpha = torch.empty((1, H, W), **f32)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        geom = torch.empty(lib.htgs_geom_bytes(P), **u8)
+        img = torch.empty(lib.htgs_image_bytes(W, H), **u8)
+        rendered = ctypes.c_int64(0)
+        nat.check(lib.htgs_forward_preprocess(
+            P, int(degree), M, nat.ptr(means3D), nat.ptr(scales), float(scale_modifier), nat.ptr(rotations),
+            nat.ptr(opacity), nat.ptr(sh), nat.ptr(cov3D_precomp), nat.ptr(colors), nat.ptr(viewmatrix),
+            nat.ptr(projmatrix), nat.ptr(campos), W, H, float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+            geom.data_ptr(), radii.data_ptr(), ctypes.byref(rendered), st), "htgs_forward_preprocess")
+        R = int(rendered.value)
+        binning = torch.empty(lib.htgs_binning_bytes(R, W, H) if R > 0 else 0, **u8)
+        nat.check(lib.htgs_forward_render(
+            P, R, W, H, nat.ptr(background), radii.data_ptr(), geom.data_ptr(), nat.ptr(binning), img.data_ptr(),
+            out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(), st), "htgs_forward_render")
+        if debug:
+            torch.cuda.synchronize(dev)  # CHECK_CUDA(..., debug) semantics, auxiliary.h:166-173
+    return R, out_color, out_depth, out_alpha, radii, geom, binning, img
+
+
+def backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                  projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
+                  geomBuffer, R, binningBuffer, imageBuffer, alphas, debug, mirror_all=True):
+    """Core of the backward.  With mirror_all=False the gradients nobody can consume (dL_dcolors on the
+    SH path, dL_dcov3D on the scale/rotation path) are neither computed into memory nor allocated and
+    come back as None."""
+    _require_cuda(means3D, "means3D")
+    dev = means3D.device
+    P = int(means3D.size(0))
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    M = int(sh.size(1)) if sh.numel() != 0 and sh.size(0) != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    has_sh, has_colors = sh.numel() != 0, colors.numel() != 0
+    has_scales, has_cov = scales.numel() != 0, cov3D_precomp.numel() != 0
+    if P == 0:
+        z = lambda *s: torch.zeros(s, **f32)
+        return z(0, 3), z(0, NUM_CHANNELS), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+    means3D, colors, scales, rotations, cov3D_precomp, sh, alphas = map(
+        _f32c, (means3D, colors, scales, rotations, cov3D_precomp, sh, alphas))
+    background, viewmatrix, projmatrix, campos = map(_f32c, (background, viewmatrix, projmatrix, campos))
+    dL_dout_color, dL_dout_depth, dL_dout_alpha = map(_f32c, (dL_dout_color, dL_dout_depth, dL_dout_alpha))
+    radii = radii.contiguous()
+    lib = nat.lib()
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        dmeans2D = torch.empty((P, 3), **f32)
+        dopacity = torch.empty((P, 1), **f32)
+        dmeans3D = torch.empty((P, 3), **f32)
+        want_colors = has_colors or mirror_all
+        want_cov = has_cov or mirror_all
+        dcolors = torch.empty((P, NUM_CHANNELS), **f32) if want_colors else None
+        dcov3D = torch.empty((P, 6), **f32) if want_cov else None
+        dsh = torch.empty((P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
+        dscales = torch.empty((P, 3), **f32) if has_scales else torch.zeros((P, 3), **f32)
+        drot = torch.empty((P, 4), **f32) if has_scales else torch.zeros((P, 4), **f32)
+        scratch = torch.empty(lib.htgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        nat.check(lib.htgs_backward(
+            P, int(degree), M, int(R), W, H, nat.ptr(background), nat.ptr(means3D), nat.ptr(sh), nat.ptr(colors),
+            nat.ptr(alphas), nat.ptr(scales), float(scale_modifier), nat.ptr(rotations), nat.ptr(cov3D_precomp),
+            nat.ptr(viewmatrix), nat.ptr(projmatrix), nat.ptr(campos), float(tan_fovx), float(tan_fovy),
+            radii.data_ptr(), geomBuffer.data_ptr(), nat.ptr(binningBuffer), imageBuffer.data_ptr(),
+            nat.ptr(dL_dout_color), nat.ptr(dL_dout_depth), nat.ptr(dL_dout_alpha), scratch.data_ptr(),
+            dmeans2D.data_ptr(), dopacity.data_ptr(), nat.ptr(dcolors), dmeans3D.data_ptr(), nat.ptr(dcov3D),
+            nat.ptr(dsh) if has_sh else None, nat.ptr(dscales) if has_scales else None,
+            nat.ptr(drot) if has_scales else None, st), "htgs_backward")
+        if debug:
+            torch.cuda.synchronize(dev)
+    return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
+                                 dL_dout_alpha, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, alphas,
+                                 debug):
+    """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:121-208).
+
+    Returns (dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3], dL_dcov3D[P,6],
+    dL_dsh[P,M,3], dL_dscales[P,3], dL_drotations[P,4])."""
+    return backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                         viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth, dL_dout_alpha, sh,
+                         degree, campos, geomBuffer, R, binningBuffer, imageBuffer, alphas, debug, mirror_all=True)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """markVisible (rasterize_points.cu:210-229): bool[P], view-space z > 0.2."""
+    _require_cuda(means3D, "means3D")
+    dev = means3D.device
+    P = int(means3D.size(0))
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    if P != 0:
+        with torch.cuda.device(dev):
+            nat.check(nat.lib().htgs_mark_visible(P, nat.ptr(_f32c(means3D)), nat.ptr(_f32c(viewmatrix)),
+                                                  nat.ptr(_f32c(projmatrix)), present.data_ptr(), _stream(dev)),
+                      "htgs_mark_visible")
+    return present

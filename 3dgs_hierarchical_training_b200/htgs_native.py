@@ -1,0 +1,102 @@
+"""ctypes binding of libhtgs.so (include/htgs.h).
+
+There is no fallback: if the CUDA library is missing or a call fails this
+module raises.  Tensors are allocated by the caller with torch; only raw
+pointers and sizes cross the boundary.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhtgs.so")
+
+c_void_p, c_int, c_int64, c_float, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
+
+_SIGNATURES = {
+    "htgs_abi_version": (c_int, []),
+    "htgs_last_error": (ctypes.c_char_p, []),
+    "htgs_geom_bytes": (c_size_t, [c_int]),
+    "htgs_image_bytes": (c_size_t, [c_int, c_int]),
+    "htgs_binning_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "htgs_backward_scratch_bytes": (c_size_t, [c_int]),
+    "htgs_geom_layout": (c_int, [c_int, ctypes.POINTER(c_size_t), c_int]),
+    "htgs_binning_layout": (c_int, [c_int64, c_int, c_int, ctypes.POINTER(c_size_t), c_int]),
+    "htgs_image_layout": (c_int, [c_int, c_int, ctypes.POINTER(c_size_t), c_int]),
+    "htgs_forward_preprocess": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,
+                                        c_int, c_void_p, c_void_p, ctypes.POINTER(c_int64), c_void_p]),
+    "htgs_forward_render": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_backward": (c_int, [c_int, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                              c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float,
+                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_mark_visible": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_sort_scratch_bytes": (c_size_t, [c_int64]),
+    "htgs_sort_pairs": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_dist2_workspace_bytes": (c_size_t, [c_int]),
+    "htgs_dist2": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+}
+
+EXPORTS = tuple(_SIGNATURES)
+ABI_VERSION = 1
+
+GEOM_FIELDS = ("means2D", "conic_opacity", "feat", "clamped", "tiles_touched", "point_offsets", "block_sums", "num_rendered")
+BIN_FIELDS = ("keys_sorted", "values_sorted", "keys_alt", "values_alt", "sort_scratch")
+IMG_FIELDS = ("ranges", "n_contrib")
+
+_lib = None
+
+
+class HtgsError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libhtgs.so once; raise loudly when it is absent (no CPU fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise HtgsError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). This plugin has no CPU or PyTorch fallback.")
+        l = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        if l.htgs_abi_version() != ABI_VERSION:
+            raise HtgsError(f"libhtgs.so ABI {l.htgs_abi_version()} != binding {ABI_VERSION}; rebuild")
+        _lib = l
+    return _lib
+
+
+def check(status, what):
+    if status != 0:
+        raise HtgsError(f"{what}: {lib().htgs_last_error().decode(errors='replace')}")
+
+
+def ptr(t):
+    """Raw pointer of a tensor, NULL for None / empty placeholders (the reference passes empty
+    tensors whose data_ptr() is 0, diff_gaussian_rasterization/__init__.py:200-210)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _layout(fn, names, *args):
+    arr = (c_size_t * len(names))()
+    n = fn(*args, arr, len(names))
+    return {names[i]: int(arr[i]) for i in range(n)}
+
+
+def geom_layout(P):
+    return _layout(lib().htgs_geom_layout, GEOM_FIELDS, P)
+
+
+def binning_layout(R, W, H):
+    return _layout(lib().htgs_binning_layout, BIN_FIELDS, R, W, H)
+
+
+def image_layout(W, H):
+    return _layout(lib().htgs_image_layout, IMG_FIELDS, W, H)

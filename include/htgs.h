@@ -1,0 +1,148 @@
+/*
+ * htgs.h -- C ABI of the B200-native differentiable Gaussian rasterizer.
+ *
+ * This is the drop-in boundary: a plain `extern "C"` shared library
+ * (3dgs_hierarchical_training_b200/libhtgs.so) with raw device pointers and
+ * sizes, no torch types.  The Python plugin mirror
+ * (3dgs_hierarchical_training_b200/diff_gaussian_rasterization, simple_knn)
+ * binds it with ctypes; INTEGRATION.md shows the binding a maintainer of the
+ * reference would add.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/submodules):
+ *   diff-gaussian-rasterization/rasterize_points.h:18-70   (torch glue)
+ *   diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:20-92
+ *   simple-knn/spatial.h:13 , simple-knn/simple_knn.h:15-19
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it;
+ *   - functions return 0 on success, non-zero on error; htgs_last_error()
+ *     returns the message of the calling thread's last failure;
+ *   - matrices use the reference's row-vector convention (flat m[4*c+r]);
+ *   - optional inputs are NULL exactly where the reference passes an empty
+ *     tensor (data_ptr()==0);
+ *   - no global mutable state; re-entrant per (device, stream).  Work buffers
+ *     are caller-owned; their sizes come from the *_bytes() queries.
+ */
+#ifndef HTGS_H_INCLUDED
+#define HTGS_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HTGS_ABI_VERSION 1
+
+int htgs_abi_version(void);
+const char* htgs_last_error(void);
+
+/* ---- work-buffer sizes (replace required<GeometryState/ImageState/BinningState>,
+ *      cuda_rasterizer/rasterizer_impl.h:66-72) ---- */
+size_t htgs_geom_bytes(int P);
+size_t htgs_image_bytes(int W, int H);
+size_t htgs_binning_bytes(int64_t R, int W, int H);
+/* scratch for the backward pass: per-Gaussian gradient accumulators */
+size_t htgs_backward_scratch_bytes(int P);
+
+/* Byte offsets of the named fields inside the opaque buffers, for parity tests
+ * and debugging.  Returns the number of fields written (<= cap). */
+enum {
+    HTGS_GEOM_MEANS2D = 0,     /* float2[P]  pixel centre                         */
+    HTGS_GEOM_CONIC_OPACITY,   /* float4[P]  conic.xyz, opacity                   */
+    HTGS_GEOM_FEAT,            /* float4[P]  r,g,b (SH colour or precomp), depth  */
+    HTGS_GEOM_CLAMPED,         /* uint8[P]   bit c set: channel c clamped at 0    */
+    HTGS_GEOM_TILES_TOUCHED,   /* uint32[P]                                       */
+    HTGS_GEOM_POINT_OFFSETS,   /* uint32[P]  inclusive prefix sum                 */
+    HTGS_GEOM_BLOCK_SUMS,      /* uint32[ceil(P/256)+1] internal                  */
+    HTGS_GEOM_NUM_RENDERED,    /* uint32[1]  R                                    */
+    HTGS_GEOM_NFIELDS
+};
+enum {
+    HTGS_BIN_KEYS_SORTED = 0,  /* uint64[R] */
+    HTGS_BIN_VALUES_SORTED,    /* uint32[R]  == point_list */
+    HTGS_BIN_KEYS_ALT,         /* uint64[R]  ping-pong partner */
+    HTGS_BIN_VALUES_ALT,       /* uint32[R] */
+    HTGS_BIN_SORT_SCRATCH,     /* histograms + look-back state */
+    HTGS_BIN_NFIELDS
+};
+enum {
+    HTGS_IMG_RANGES = 0,       /* uint2[tiles] */
+    HTGS_IMG_N_CONTRIB,        /* uint32[W*H]  */
+    HTGS_IMG_NFIELDS
+};
+int htgs_geom_layout(int P, size_t* offsets, int cap);
+int htgs_binning_layout(int64_t R, int W, int H, size_t* offsets, int cap);
+int htgs_image_layout(int W, int H, size_t* offsets, int cap);
+
+/* ---- forward, phase 1: per-Gaussian preprocess + tile-count prefix sum ----
+ * Replaces FORWARD::preprocess + cub::DeviceScan::InclusiveSum + the blocking
+ * 4-byte copy (cuda_rasterizer/rasterizer_impl.cu:249-282, forward.cu:155-256).
+ * Writes radii[P] (0 for culled) and the geometry buffer, then waits for the
+ * stream and stores R = number of (Gaussian, tile) instances in
+ * *num_rendered_host so the caller can size the binning buffer. */
+int htgs_forward_preprocess(int P, int D, int M,
+                            const float* means3D, const float* scales, float scale_modifier,
+                            const float* rotations, const float* opacities, const float* shs,
+                            const float* cov3D_precomp, const float* colors_precomp,
+                            const float* viewmatrix, const float* projmatrix, const float* campos,
+                            int W, int H, float tanfovx, float tanfovy, int prefiltered,
+                            void* geom_buf, int* radii, int64_t* num_rendered_host, void* stream);
+
+/* ---- forward, phase 2: key generation, radix sort, tile ranges, blend ----
+ * Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + memset +
+ * identifyTileRanges + FORWARD::render (rasterizer_impl.cu:284-336,
+ * forward.cu:261-381).  out_color[3,H,W], out_depth[H,W], out_alpha[H,W]. */
+int htgs_forward_render(int P, int64_t R, int W, int H, const float* background,
+                        const int* radii, void* geom_buf, void* binning_buf, void* image_buf,
+                        float* out_color, float* out_depth, float* out_alpha, void* stream);
+
+/* ---- backward ----
+ * Replaces Rasterizer::backward (rasterizer_impl.cu:343-447; backward.cu).
+ * Every non-NULL dL_* output is fully written (zeros for culled Gaussians), so
+ * the caller may allocate them uninitialised (the reference zero-fills ten
+ * tensors per call, rasterize_points.cu:158-167).
+ *   dL_dmeans2D[P,3] dL_dopacity[P] dL_dmeans3D[P,3]            always
+ *   dL_dcolors[P,3]   when colors_precomp != NULL (else may be NULL)
+ *   dL_dsh[P,M,3]     when shs != NULL
+ *   dL_dscales[P,3], dL_drotations[P,4]  when scales != NULL
+ *   dL_dcov3D[P,6]    when cov3D_precomp != NULL (else may be NULL)          */
+int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* background,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* alphas, const float* scales, float scale_modifier,
+                  const float* rotations, const float* cov3D_precomp,
+                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                  float tanfovx, float tanfovy, const int* radii,
+                  const void* geom_buf, const void* binning_buf, const void* image_buf,
+                  const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+                  void* scratch,
+                  float* dL_dmeans2D, float* dL_dopacity, float* dL_dcolors, float* dL_dmeans3D,
+                  float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+                  void* stream);
+
+/* Replaces Rasterizer::markVisible (rasterizer_impl.cu:141-153): present[i] =
+ * view-space z > 0.2.  `present` is uint8/bool[P]. */
+int htgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                      uint8_t* present, void* stream);
+
+/* Stand-alone stable LSD radix sort of (uint64 key, uint32 value) pairs on key
+ * bits [0, end_bit), the contract of cub::DeviceRadixSort::SortPairs as used
+ * at rasterizer_impl.cu:304-309.  keys_in/values_in are clobbered.  scratch
+ * comes from htgs_sort_scratch_bytes(n). */
+size_t htgs_sort_scratch_bytes(int64_t n);
+int htgs_sort_pairs(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* values_in,
+                    uint64_t* keys_out, uint32_t* values_out, void* scratch, void* stream);
+
+/* ---- simple-knn ----
+ * Replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:15-26,
+ * simple_knn.cu:186-222): out[i] = mean of the squared distances from point i
+ * to its 3 nearest other points.  No allocation, no host sync. */
+size_t htgs_dist2_workspace_bytes(int P);
+int htgs_dist2(int P, const float* points, float* out, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HTGS_H_INCLUDED */
