@@ -1,8 +1,9 @@
 // Per-Gaussian projection math with an explicit, contraction-proof operation
 // order.  radii, tile rectangles and the depth bits of the sort keys must be
-// bit-identical to the reference, whose rounding is fixed by how nvcc contracts
-// its glm expressions (PTX of cuda_rasterizer/forward.cu:74-256, auxiliary.h:41-77
-// at -O3, default -fmad).  Writing every operation as an _rn intrinsic stops
+// bit-identical to the reference, whose rounding is fixed by how nvcc AND ptxas
+// contract its glm expressions (SASS of cuda_rasterizer/forward.cu:74-256,
+// auxiliary.h:41-77 for sm_100a at -O3, default -fmad; the PTX alone is not enough:
+// mul.f32/add.f32 without .rn are fused further by ptxas).  Writing every operation as an _rn intrinsic stops
 // the compiler from fusing or re-associating anything here.
 #pragma once
 #include "common.cuh"
@@ -44,12 +45,15 @@ __device__ __forceinline__ void get_rect(float px, float py, int radius, int gx,
 __device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float4 q, float* cov) {
     const float sx = MU(mod, s0), sy = MU(mod, s1), sz = MU(mod, s2);
     const float r = q.x, x = q.y, y = q.z, z = q.w;
+    // ptxas contracts the reference's mul/add pairs here: one product of each pair is rounded
+    // (xz, rx, rz), the other is fused (SASS of preprocessCUDA, sm_100a).
     const float yy = MU(y, y), zz = MU(z, z);
-    const float xy = MU(x, y), rz = MU(r, z), xz = MU(x, z), ry = MU(r, y), yz = MU(y, z), rx = MU(r, x);
+    const float xz = MU(x, z), rx = MU(r, x), rz = MU(r, z);
     const float yy_zz = AD(yy, zz);
     const float xx_zz = FM(x, x, zz);
     const float xx_yy = FM(x, x, yy);
-    const float d0 = SB(xy, rz), d1 = AD(ry, xz), d2 = AD(xy, rz), d3 = SB(yz, rx), d4 = SB(xz, ry), d5 = AD(rx, yz);
+    const float d0 = FM(x, y, -rz), d1 = FM(r, y, xz), d2 = FM(x, y, rz), d3 = FM(y, z, -rx), d4 = FM(-r, y, xz),
+                d5 = FM(y, z, rx);
     const float R00 = SB(1.0f, AD(yy_zz, yy_zz));
     const float R01 = AD(d0, d0);
     const float R02 = AD(d1, d1);
@@ -125,10 +129,11 @@ __device__ __forceinline__ void ewa_cov2d(const Ewa& e, const float* c, float& a
 
 // The Gaussian falloff exponent of one (pixel, Gaussian) pair, in the exact
 // order nvcc gives forward.cu:339 / backward.cu:525:
-//   power = (fma(dx, dx*cx, dy*(dy*cz)) * -0.5f) - dy*(dx*cy)
+//   power = fma(fma(dx, dx*cx, dy*(dy*cz)), -0.5f, -(dy*(dx*cy)))
+// (the PTX shows mul/sub; ptxas fuses them -- SASS: FFMA R14, R14, -0.5, -R29)
 __device__ __forceinline__ float pair_power(float dx, float dy, float cx, float cy, float cz) {
     const float q = FM(dx, MU(dx, cx), MU(dy, MU(dy, cz)));
-    return SB(MU(q, -0.5f), MU(dy, MU(dx, cy)));
+    return FM(q, -0.5f, -MU(dy, MU(dx, cy)));
 }
 
 // SH basis constants (auxiliary.h:22-39)

@@ -13,7 +13,7 @@
 
 namespace htgs {
 
-// SH colour, forward.cu:20-71, in the operation order of the reference's PTX.
+// SH colour, forward.cu:20-71, in the operation order of the reference's SASS (sm_100a).
 // NCOEF floats of `sh` are valid ((D+1)^2 * 3).
 template <int D>
 __device__ __forceinline__ void sh_to_rgb(const float* sh, float x, float y, float z, float* res) {
@@ -23,9 +23,9 @@ __device__ __forceinline__ void sh_to_rgb(const float* sh, float x, float y, flo
         const float k1 = MU(y, HTGS_SH_C1), k2 = MU(z, HTGS_SH_C1), k3 = MU(x, HTGS_SH_C1);
 #pragma unroll
         for (int c = 0; c < 3; c++) {
-            float t = SB(res[c], MU(k1, sh[3 + c]));
+            float t = FM(-k1, sh[3 + c], res[c]);
             t = FM(k2, sh[6 + c], t);
-            res[c] = SB(t, MU(k3, sh[9 + c]));
+            res[c] = FM(-k3, sh[9 + c], t);
         }
     }
     if (D > 1) {
@@ -48,15 +48,14 @@ __device__ __forceinline__ void sh_to_rgb(const float* sh, float x, float y, flo
             res[c] = t;
         }
         if (D > 2) {
-            const float xx3 = MU(xx, 3.0f), yy3 = MU(yy, 3.0f), zz4 = MU(zz, 4.0f);
-            const float k9 = MU(MU(y, HTGS_SH_C3_0), SB(xx3, yy));
+            const float k9 = MU(MU(y, HTGS_SH_C3_0), FM(xx, 3.0f, -yy));
             const float k10 = MU(z, MU(xy, HTGS_SH_C3_1));
-            const float m4 = SB(SB(zz4, xx), yy);
+            const float m4 = SB(FM(zz, 4.0f, -xx), yy);
             const float k11 = MU(MU(y, HTGS_SH_C3_2), m4);
-            const float k12 = MU(MU(z, HTGS_SH_C3_3), SB(SB(zz2, xx3), yy3));
+            const float k12 = MU(MU(z, HTGS_SH_C3_3), FM(yy, -3.0f, FM(xx, -3.0f, zz2)));
             const float k13 = MU(MU(x, HTGS_SH_C3_4), m4);
             const float k14 = MU(MU(z, HTGS_SH_C3_5), xx_yy);
-            const float k15 = MU(MU(x, HTGS_SH_C3_6), SB(xx, yy3));
+            const float k15 = MU(MU(x, HTGS_SH_C3_6), FM(yy, -3.0f, xx));
 #pragma unroll
             for (int c = 0; c < 3; c++) {
                 float t = res[c];
@@ -143,12 +142,12 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
             const Ewa e = ewa_setup(px, py, pz, vm, focal_x, focal_y, tanfovx, tanfovy);
             float a, b, c;
             ewa_cov2d(e, cov3, a, b, c);
-            const float det = SB(MU(a, c), MU(b, b));
+            const float det = FM(a, c, -MU(b, b));
             if (det == 0.0f) break;
             const float det_inv = __frcp_rn(det);
             const float conx = MU(c, det_inv), cony = MU(det_inv, -b), conz = MU(a, det_inv);
             const float mid = MU(AD(a, c), 0.5f);
-            const float sq = __fsqrt_rn(fmaxf(SB(MU(mid, mid), det), 0.1f));
+            const float sq = __fsqrt_rn(fmaxf(FM(mid, mid, -det), 0.1f));
             const float lam = fmaxf(AD(mid, sq), SB(mid, sq));
             const int rad = (int)ceilf(MU(__fsqrt_rn(lam), 3.0f));
             const float pix_x = ndc2pix(projx, W), pix_y = ndc2pix(projy, H);
