@@ -67,6 +67,28 @@ ImgView img_view(void* base, int W, int H) {
     return v;
 }
 
+// ---- per-stage timing: explicit, process-wide measurement aid (the one piece of global state;
+// not thread-safe, off by default) ----
+static bool g_prof_on = false;
+static const int PROF_CAP = 8192;
+static cudaEvent_t g_prof_ev[PROF_CAP][2];
+static int g_prof_stage[PROF_CAP];
+static int g_prof_n = 0, g_prof_created = 0;
+
+StageTimer::StageTimer(int stage, cudaStream_t s) : slot(-1), st(s) {
+    if (!g_prof_on || g_prof_n >= PROF_CAP) return;
+    if (g_prof_n >= g_prof_created) {
+        if (cudaEventCreate(&g_prof_ev[g_prof_n][0]) != cudaSuccess || cudaEventCreate(&g_prof_ev[g_prof_n][1]) != cudaSuccess) return;
+        g_prof_created = g_prof_n + 1;
+    }
+    slot = g_prof_n++;
+    g_prof_stage[slot] = stage;
+    cudaEventRecord(g_prof_ev[slot][0], st);
+}
+StageTimer::~StageTimer() {
+    if (slot >= 0) cudaEventRecord(g_prof_ev[slot][1], st);
+}
+
 static bool aligned256(const void* p) { return (reinterpret_cast<size_t>(p) & 255) == 0; }
 
 }  // namespace htgs
@@ -76,6 +98,35 @@ using namespace htgs;
 extern "C" {
 
 int htgs_abi_version(void) { return HTGS_ABI_VERSION; }
+
+void htgs_profile_enable(int on) {
+    g_prof_on = on != 0;
+    g_prof_n = 0;
+}
+
+int htgs_profile_read(double* ms_sum, int* counts, int cap) {
+    for (int i = 0; i < cap; i++) { ms_sum[i] = 0.0; counts[i] = 0; }
+    for (int i = 0; i < g_prof_n; i++) {
+        if (cudaEventSynchronize(g_prof_ev[i][1]) != cudaSuccess) { set_error("htgs_profile_read: event sync failed"); return -1; }
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_prof_ev[i][0], g_prof_ev[i][1]) != cudaSuccess) { set_error("htgs_profile_read: elapsed failed"); return -1; }
+        const int s = g_prof_stage[i];
+        if (s < cap) { ms_sum[s] += ms; counts[s]++; }
+    }
+    g_prof_n = 0;
+    return ST_COUNT;
+}
+
+int htgs_blend_stats(int P, int64_t R, int W, int H, const void* geom_buf, const void* binning_buf, const void* image_buf,
+                     unsigned long long* stats3, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (P <= 0 || !geom_buf || !image_buf || !stats3) { set_error("htgs_blend_stats: bad arguments"); return 1; }
+    GeomView g = geom_view(const_cast<void*>(geom_buf), P);
+    ImgView img = img_view(const_cast<void*>(image_buf), W, H);
+    BinView b = bin_view(const_cast<void*>(binning_buf), R, W, H);
+    HTGS_CUDA_CHECK(cudaMemsetAsync(stats3, 0, 3 * sizeof(unsigned long long), st));
+    return launch_blend_stats(W, H, img.ranges, b.values_sorted, g, stats3, st);
+}
 const char* htgs_last_error(void) { return g_error; }
 
 size_t htgs_geom_bytes(int P) { return geom_view(nullptr, P < 0 ? 0 : P).bytes; }
@@ -134,9 +185,11 @@ int htgs_forward_preprocess(int P, int D, int M, const float* means3D, const flo
     if (!aligned256(geom_buf)) { set_error("htgs_forward_preprocess: geom_buf must be 256-byte aligned"); return 1; }
     if (rotations && (reinterpret_cast<size_t>(rotations) & 15)) { set_error("htgs_forward_preprocess: rotations must be 16-byte aligned"); return 1; }
     GeomView g = geom_view(geom_buf, P);
+    { StageTimer t(ST_PREPROCESS, st);
     if (launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp, colors_precomp,
-                          viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, g, radii, st)) return 1;
-    if (launch_scan_block_sums(P, g, st)) return 1;
+                          viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, g, radii, st)) return 1; }
+    { StageTimer t(ST_SCAN, st);
+    if (launch_scan_block_sums(P, g, st)) return 1; }
     uint32_t r32 = 0;
     HTGS_CUDA_CHECK(cudaMemcpyAsync(&r32, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     HTGS_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -170,12 +223,16 @@ int htgs_forward_render(int P, int64_t R, int W, int H, const float* background,
         uint32_t* v0 = (passes & 1) ? b.values_alt : b.values_sorted;
         uint64_t* k1 = (passes & 1) ? b.keys_sorted : b.keys_alt;
         uint32_t* v1 = (passes & 1) ? b.values_sorted : b.values_alt;
-        if (launch_make_keys(P, W, H, radii, g, k0, v0, st)) return 1;
-        if (sort_pairs(R, end_bit, k0, v0, k1, v1, b.sort_scratch, st)) return 1;
+        { StageTimer t(ST_MAKE_KEYS, st);
+        if (launch_make_keys(P, W, H, radii, g, k0, v0, st)) return 1; }
+        { StageTimer t(ST_SORT, st);
+        if (sort_pairs(R, end_bit, k0, v0, k1, v1, b.sort_scratch, st)) return 1; }
     }
-    if (launch_tile_ranges(R, W, H, b.keys_sorted, img.ranges, st)) return 1;
+    { StageTimer t(ST_TILE_RANGES, st);
+    if (launch_tile_ranges(R, W, H, b.keys_sorted, img.ranges, st)) return 1; }
+    { StageTimer t(ST_BLEND_FWD, st);
     if (launch_blend_forward(W, H, img.ranges, b.values_sorted, g, background, out_color, out_depth, out_alpha,
-                             img.n_contrib, st)) return 1;
+                             img.n_contrib, st)) return 1; }
     return 0;
 }
 
@@ -209,12 +266,15 @@ int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* bac
     ImgView img = img_view(const_cast<void*>(image_buf), W, H);
     BinView b = bin_view(const_cast<void*>(binning_buf), R, W, H);
     float* gacc = reinterpret_cast<float*>(scratch);
-    HTGS_CUDA_CHECK(cudaMemsetAsync(gacc, 0, (size_t)P * 12 * sizeof(float), st));
+    { StageTimer t(ST_ZERO_ACC, st);
+    HTGS_CUDA_CHECK(cudaMemsetAsync(gacc, 0, (size_t)P * 12 * sizeof(float), st)); }
     if (R > 0) {
+        StageTimer t(ST_BLEND_BWD, st);
         if (launch_blend_backward(P, W, H, img.ranges, b.values_sorted, g, background, alphas, img.n_contrib, dL_dout_color,
                                   dL_dout_depth, dL_dout_alpha, gacc, st)) return 1;
     }
     // the SH path feeds dL/dcolour into dL/dsh; only the precomputed-colour path returns it
+    StageTimer t(ST_GEOM_BWD, st);
     if (launch_geom_backward(P, D, M, means3D, radii, shs, colors_precomp, scales, scale_modifier, rotations, cov3D_precomp,
                              viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, g, gacc, dL_dmeans2D, dL_dopacity,
                              dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, st)) return 1;

@@ -15,11 +15,17 @@ namespace htgs {
 
 constexpr int FWD_BATCH = 256;
 
+// STATS=true is a measurement variant: same traversal, no image writes; it adds to stats[0] the
+// pair tests the reference's one-thread-per-pixel loop would execute (list entries walked
+// until the pixel saturates), to stats[1] the blended pairs, to stats[2] the pair tests this
+// kernel executes after reach-mask culling.
+template <bool STATS>
 __global__ void __launch_bounds__(HTGS_TILE_PIX)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                      const float4* __restrict__ feat, const float* __restrict__ bg, float* __restrict__ out_color,
-                     float* __restrict__ out_depth, float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib) {
+                     float* __restrict__ out_depth, float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
+                     unsigned long long* __restrict__ stats) {
     __shared__ float4 s_co[FWD_BATCH];
     __shared__ float4 s_feat[FWD_BATCH];
     __shared__ float2 s_xy[FWD_BATCH];
@@ -38,6 +44,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, dsum = 0.f;
     uint32_t last_contributor = 0;
+    uint32_t st_blended = 0, st_tested = 0, st_done_pos = 0;
 
     for (int base = 0; base < n; base += FWD_BATCH) {
         // leave when every pixel of the tile is saturated (forward.cu:313-315)
@@ -62,6 +69,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 const int idx = c0 + __ffs(m) - 1;
                 m &= m - 1;
                 if (done) continue;
+                if (STATS) st_tested++;
                 const float2 xy = s_xy[idx];
                 const float4 co = s_co[idx];
                 const float dx = SB(xy.x, pxf), dy = SB(xy.y, pyf);
@@ -70,7 +78,11 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 const float alpha = fminf(0.99f, MU(co.w, expf(power)));
                 if (alpha < 1.0f / 255.0f) continue;
                 const float test_T = MU(T, SB(1.0f, alpha));
-                if (test_T < 0.0001f) { done = true; continue; }
+                if (test_T < 0.0001f) {
+                    done = true;
+                    if (STATS) st_done_pos = (uint32_t)(base + idx + 1);
+                    continue;
+                }
                 const float4 f = s_feat[idx];
                 C0 = FM(T, MU(alpha, f.x), C0);
                 C1 = FM(T, MU(alpha, f.y), C1);
@@ -79,9 +91,18 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 dsum = FM(T, MU(alpha, f.w), dsum);
                 T = test_T;
                 last_contributor = (uint32_t)(base + idx + 1);
+                if (STATS) st_blended++;
             }
             if (__all_sync(0xffffffffu, done)) break;
         }
+    }
+    if (STATS) {
+        if (inside) {
+            atomicAdd(&stats[0], (unsigned long long)(st_done_pos ? st_done_pos : (uint32_t)n));
+            atomicAdd(&stats[1], (unsigned long long)st_blended);
+            atomicAdd(&stats[2], (unsigned long long)st_tested);
+        }
+        return;
     }
     if (inside) {
         const size_t pix = (size_t)py * W + px;
@@ -99,9 +120,19 @@ int launch_blend_forward(int W, int H, const uint2* ranges, const uint32_t* poin
                          const float* bg, float* out_color, float* out_depth, float* out_alpha,
                          uint32_t* n_contrib, cudaStream_t st) {
     const dim3 grid((W + HTGS_TILE - 1) / HTGS_TILE, (H + HTGS_TILE - 1) / HTGS_TILE);
-    blend_forward_kernel<<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, g.means2D, g.conic_opacity, g.feat, bg,
-                                                         out_color, out_depth, out_alpha, n_contrib);
+    blend_forward_kernel<false><<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, g.means2D, g.conic_opacity,
+                                                                g.feat, bg, out_color, out_depth, out_alpha, n_contrib,
+                                                                nullptr);
     HTGS_LAUNCH_CHECK("blend_forward_kernel");
+    return 0;
+}
+
+int launch_blend_stats(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                       unsigned long long* stats, cudaStream_t st) {
+    const dim3 grid((W + HTGS_TILE - 1) / HTGS_TILE, (H + HTGS_TILE - 1) / HTGS_TILE);
+    blend_forward_kernel<true><<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, g.means2D, g.conic_opacity, g.feat,
+                                                               nullptr, nullptr, nullptr, nullptr, nullptr, stats);
+    HTGS_LAUNCH_CHECK("blend_forward_kernel<stats>");
     return 0;
 }
 

@@ -75,6 +75,8 @@ int launch_tile_ranges(int64_t R, int W, int H, const uint64_t* keys_sorted, uin
 int launch_blend_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                          const float* bg, float* out_color, float* out_depth, float* out_alpha,
                          uint32_t* n_contrib, cudaStream_t st);
+int launch_blend_stats(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                       unsigned long long* stats, cudaStream_t st);
 int launch_blend_backward(int P, int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                           const float* bg, const float* alphas, const uint32_t* n_contrib, const float* dL_dpix,
                           const float* dL_ddepth, const float* dL_dalpha, float* gacc, cudaStream_t st);
@@ -93,5 +95,15 @@ int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t*
 int sort_num_passes(int end_bit);
 
 uint32_t higher_msb(uint32_t n);
+
+// ---- optional per-stage timing (htgs_profile_*) ----
+enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_MAKE_KEYS, ST_SORT, ST_TILE_RANGES, ST_BLEND_FWD, ST_ZERO_ACC, ST_BLEND_BWD,
+             ST_GEOM_BWD, ST_COUNT };
+struct StageTimer {  // records a CUDA event pair around a stage when profiling is on
+    StageTimer(int stage, cudaStream_t st);
+    ~StageTimer();
+    int slot;
+    cudaStream_t st;
+};
 
 }  // namespace htgs

@@ -34,6 +34,9 @@ _SIGNATURES = {
     "htgs_mark_visible": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_sort_scratch_bytes": (c_size_t, [c_int64]),
     "htgs_sort_pairs": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_profile_enable": (None, [c_int]),
+    "htgs_profile_read": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int), c_int]),
+    "htgs_blend_stats": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_dist2_workspace_bytes": (c_size_t, [c_int]),
     "htgs_dist2": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
 }
@@ -88,6 +91,22 @@ def _layout(fn, names, *args):
     arr = (c_size_t * len(names))()
     n = fn(*args, arr, len(names))
     return {names[i]: int(arr[i]) for i in range(n)}
+
+
+STAGES = ("preprocess", "scan", "make_keys", "sort", "tile_ranges", "blend_fwd", "zero_acc", "blend_bwd", "geom_bwd")
+
+
+def profile_enable(on=True):
+    lib().htgs_profile_enable(1 if on else 0)
+
+
+def profile_read():
+    """{stage: (total_ms, launches)} since the last read; waits for the recorded events."""
+    ms = (ctypes.c_double * len(STAGES))()
+    cnt = (c_int * len(STAGES))()
+    if lib().htgs_profile_read(ms, cnt, len(STAGES)) < 0:
+        raise HtgsError(lib().htgs_last_error().decode(errors="replace"))
+    return {STAGES[i]: (float(ms[i]), int(cnt[i])) for i in range(len(STAGES))}
 
 
 def geom_layout(P):

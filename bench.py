@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd rasterize throughput of the B200-native plugin (BASELINE.json metric).
+
+    python bench.py [--gpus N --steps K --warmup W] [--impl ours|reference|refcuda] [--workload config3]
+
+A "step" is one forward + backward of the drop-in `diff_gaussian_rasterization` plugin on one view
+of the named synthetic workload (default: config3 = 1M Gaussians, SH degree 3, 1920x1080, the shape
+the metric is quoted on), with fixed upstream gradients for colour, depth and alpha.  With N>1 ranks
+(torchrun) every rank renders its own camera of the same scene (view-parallel, weak scaling) and the
+step ends with one NCCL all-reduce of the flat 59-float/Gaussian parameter gradient.
+
+impl:
+  ours       this repository's CUDA path (the default arm).
+  reference  the reference has no CPU rasterizer; this arm times the CPU oracle port
+             (oracle/htgs_oracle.c, all host threads) on the same workload and metric.
+  refcuda    extra, outside the contract: the UNMODIFIED reference CUDA rasterizer built into
+             oracle/_ref, same harness -- the A/B the north star asks for.
+One JSON line is printed by rank 0.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GPU_LAUNCHES_FWD = 12  # preprocess, scan, make_keys, hist, scan_hist, 6 x onesweep (config3: 45 key bits), ranges... see below
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "refcuda"])
+    ap.add_argument("--workload", default="config3")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons with nvidia-smi while the timed region runs."""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def load_plugin():
+    pkg = importlib.import_module("3dgs_hierarchical_training_b200")
+    pkg.install()
+    import htgs_native as nat
+    import htgs_synthetic as syn
+    import diff_gaussian_rasterization as dgr
+    return nat, syn, dgr
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json)", d
+    return 6650.0, "fallback (B200_PROFILING.md)", {}
+
+
+def stage_bytes(P, P_vis, R, tiles, M, passes):
+    """Algorithmic HBM bytes per launch of the streaming stages."""
+    sh = 12 * M
+    return {
+        "preprocess": P * 20 + P_vis * (28 + 4 + sh + 8 + 16 + 16 + 1),
+        "make_keys": P * 8 + P_vis * 20 + 12 * R,
+        "sort": R * (8 + passes * 24),
+        "tile_ranges": 8 * tiles,
+        "geom_bwd": P * 4 + P_vis * (48 + 12 + 28 + sh + 1) + P * (12 + 4 + 12 + sh + 12 + 16),
+    }
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    nat, syn, dgr = load_plugin()
+    nat.lib()  # fail loudly here if the CUDA library is missing
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    cfg, scene, cam0, up = syn.make_config(args.workload, device="cpu")
+    P, W, H = cfg["P"], cfg["W"], cfg["H"]
+    # every rank renders its own view of the shared scene
+    yaw = 3.0 * (rank - (world - 1) / 2.0)
+    cam_h = syn.make_camera(W, H, yaw_deg=yaw)
+    params = {k: v.to(dev).requires_grad_(True) for k, v in scene.items()}
+    bg = torch.zeros(3, device=dev)  # HT renderers use a black background (trainer/ht3dgs_trainer.py:47-53)
+    up_d = {k: v.to(dev) for k, v in up.items()}
+    cam_d = {k: (v.to(dev) if hasattr(v, "to") else v) for k, v in cam_h.items()}
+    flat = torch.zeros(P * 59, device=dev) if world > 1 else None
+
+    def settings(cam):
+        return dgr.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+                                                 bg=bg, scale_modifier=1.0, viewmatrix=cam["viewmatrix"],
+                                                 projmatrix=cam["projmatrix"], sh_degree=3, campos=cam["campos"],
+                                                 prefiltered=False, debug=False)
+
+    def step(cam, upg):
+        for p in params.values():
+            p.grad = None
+        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        rast = dgr.GaussianRasterizer(settings(cam))
+        color, radii, depth, alpha = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                                          shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        torch.autograd.backward((color, depth, alpha), (upg["dL_dcolor"], upg["dL_ddepth"], upg["dL_dalpha"]))
+        if world > 1:
+            o = 0
+            for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+                g = params[k].grad.reshape(-1)
+                flat[o:o + g.numel()].copy_(g)
+                o += g.numel()
+            dist.all_reduce(flat)
+        return color, radii
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        step(cam_d, up_d)
+    barrier()
+
+    # ---- device-timed region: inputs resident in HBM ----
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    nat.profile_enable(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        color, radii = step(cam_d, up_d)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    stages = nat.profile_read()
+    nat.profile_enable(False)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_per_step = ms_total / args.steps
+
+    # ---- end-to-end through the public plugin API with HOST buffers ----
+    e2e = None
+    if not args.no_e2e:
+        host = {k: v.pin_memory() for k, v in up.items()}
+        host_cam = {k: cam_h[k].pin_memory() for k in ("viewmatrix", "projmatrix", "campos")}
+        h2d = sum(v.numel() * 4 for v in host.values()) + sum(v.numel() * 4 for v in host_cam.values())
+        result = torch.zeros(1, dtype=torch.float64).pin_memory()
+
+        def e2e_step():
+            upg = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+            cam = dict(cam_h)
+            for k, v in host_cam.items():
+                cam[k] = v.to(dev, non_blocking=True)
+            color, radii = step(cam, upg)
+            s = (color.double().sum() + params["opacities"].grad.double().sum()).reshape(1)
+            result.copy_(s, non_blocking=False)  # device->host read of the step's scalar result
+            return float(result[0])
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * args.steps / dt, "unit": "views/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 8,
+               "ms_per_step": 1e3 * dt / args.steps}
+
+    if rank != 0:
+        return None
+
+    # ---- workload counters + roofline (rank 0) ----
+    lib = nat.lib()
+    import ctypes
+    from diff_gaussian_rasterization import _C
+    empty = torch.Tensor([])
+    with torch.no_grad():
+        R, color, depth, alpha, radii, geom, binning, img = _C.rasterize_gaussians(
+            bg, params["means3D"], empty, params["opacities"], params["scales"], params["rotations"], 1.0, empty,
+            cam_d["viewmatrix"], cam_d["projmatrix"], cam_d["tanfovx"], cam_d["tanfovy"], H, W, params["shs"], 3,
+            cam_d["campos"], False, False)
+        stats = torch.zeros(3, dtype=torch.int64, device=dev)
+        nat.check(lib.htgs_blend_stats(P, R, W, H, geom.data_ptr(), nat.ptr(binning), img.data_ptr(), stats.data_ptr(),
+                                       ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "htgs_blend_stats")
+        n_ref_tested, n_blended, n_ours_tested = [int(x) for x in stats.cpu()]
+        P_vis = int((radii > 0).sum())
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    key_bits = 32 + max(1, (tiles).bit_length())
+    passes = (key_bits + 7) // 8
+    hbm_peak, peak_src, peaks = measured_peaks()
+    per = {k: (ms / max(c, 1)) for k, (ms, c) in stages.items()}
+    by = stage_bytes(P, P_vis, R, tiles, 16, passes)
+    stage_report = {}
+    for k, ms in per.items():
+        ent = {"ms": round(ms, 4)}
+        if k in by and ms > 0:
+            ent["algorithmic_GBps"] = round(by[k] / (ms * 1e-3) / 1e9, 1)
+            ent["frac_of_hbm_peak"] = round(ent["algorithmic_GBps"] / hbm_peak, 3)
+        stage_report[k] = ent
+    sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    # FP32-issue model of the two blend kernels: FLOPs of the reference's per-pair arithmetic
+    # (DESIGN.md section 4): 22 per tested pair + 11 per blended pair forward; 22 + 70 backward.
+    fp32_peak_tflops = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+    dom = max(("blend_bwd", "blend_fwd", "sort", "preprocess", "geom_bwd"), key=lambda k: per.get(k, 0.0))
+    if dom in ("blend_bwd", "blend_fwd"):
+        flops = (22 * n_ref_tested + 11 * n_blended) if dom == "blend_fwd" else (22 * n_ref_tested + 70 * n_blended)
+        ach = flops / (per[dom] * 1e-3) / 1e12
+        roofline = {"kernel": dom, "bound": "fp32", "achieved": round(ach, 3), "peak": round(fp32_peak_tflops, 2),
+                    "unit": "TFLOP/s", "frac": round(ach / fp32_peak_tflops, 4), "traffic": None,
+                    "peak_source": f"148 SMs x 128 lanes x 2 x {sm_mhz} MHz (clock sampled during the run); no tensor cores on this path",
+                    "work": "reference-algorithm FLOPs of the pairs the reference loop tests/blends"}
+    else:
+        ach = by[dom] / (per[dom] * 1e-3) / 1e9
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak, "unit": "GB/s",
+                    "frac": round(ach / hbm_peak, 4), "traffic": None, "peak_source": peak_src}
+    out = {
+        "metric": "fwd+bwd rasterize views/s (1M Gaussians SH3 1080p per view)" if args.workload == "config3" else f"fwd+bwd rasterize views/s ({args.workload})",
+        "value": world * 1e3 / ms_per_step, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "gaussians_per_s": world * P * 1e3 / ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "P": P, "W": W, "H": H, "sh_degree": 3, "views_per_step_per_gpu": 1,
+                   "P_visible": P_vis, "R_instances": int(R), "pairs_tested_reference_loop": n_ref_tested,
+                   "pairs_tested_after_culling": n_ours_tested, "pairs_blended": n_blended,
+                   "l2": "inputs+outputs per step (~0.7 GB) exceed the 126 MB L2; no explicit flush",
+                   "parallelism": f"view-parallel dp{world}" + (" + NCCL all-reduce of 59 f32/Gaussian" if world > 1 else "")},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (5 + passes + 2 + 2),
+        "roofline": roofline, "roofline_stages": stage_report, "impl": "ours",
+    }
+    if not args.no_cpu_baseline and world == 1:
+        out["cpu_baseline"] = cpu_baseline(args.workload, steps=1)
+    return out
+
+
+def cpu_baseline(workload, steps=1, warm=False):
+    """Times the CPU oracle port (all host threads) on one full fwd+bwd view of the workload."""
+    pkg = importlib.import_module("3dgs_hierarchical_training_b200")
+    pkg.install()
+    import htgs_synthetic as syn
+    import numpy as np
+    from oracle import golden
+    cfg, scene, cam, up = syn.make_config(workload)
+    bg = np.zeros(3, np.float32)
+    sc = {k: v.numpy() for k, v in scene.items()}
+    upn = {k: v.numpy() for k, v in up.items()}
+
+    def one():
+        st = golden.forward(sc["means3D"], sc["opacities"], cam, bg, 3, shs=sc["shs"], scales=sc["scales"], rotations=sc["rotations"])
+        golden.backward(st, upn["dL_dcolor"], upn["dL_ddepth"], upn["dL_dalpha"])
+
+    if warm:
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": 1.0 / dt, "unit": "views/s", "ms_per_step": dt * 1e3, "cores": golden.num_threads(), "kind": "port",
+            "sample": f"{steps} full fwd+bwd view(s) of {workload} ({cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}), OpenMP over tiles/Gaussians"}
+
+
+def run_reference(args, rank):
+    """Contract arm `--impl reference`: the reference has no CPU implementation of this path, so the
+    CPU oracle port is timed (bounded: each step is one full view; few steps)."""
+    if rank != 0:
+        return None
+    steps = max(1, min(args.steps, 3))
+    cb = cpu_baseline(args.workload, steps=steps, warm=args.warmup > 0)
+    cfg_name = args.workload
+    pkg = importlib.import_module("3dgs_hierarchical_training_b200")
+    pkg.install()
+    import htgs_synthetic as syn
+    c = syn.CONFIGS[cfg_name]
+    return {"metric": "fwd+bwd rasterize views/s (1M Gaussians SH3 1080p per view)" if cfg_name == "config3" else f"fwd+bwd rasterize views/s ({cfg_name})",
+            "value": cb["value"], "unit": "views/s", "n_gpus": args.gpus, "steps": steps, "warmup": 1 if args.warmup > 0 else 0,
+            "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": cfg_name, "P": c["P"], "W": c["W"], "H": c["H"], "sh_degree": 3},
+            "impl": "reference", "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference has no CPU rasterizer; this is the CPU oracle port (oracle/htgs_oracle.c) on all host threads"}
+
+
+def run_refcuda(args, rank, local_rank):
+    """Extra arm: the unmodified reference CUDA rasterizer (oracle/_ref), same scene and upstream gradients."""
+    if rank != 0:
+        return None
+    import torch
+    from oracle import refcuda
+    if not refcuda.available():
+        return {"impl": "refcuda", "unavailable": "oracle/_ref not built (run `make -C oracle ref` where /root/reference exists)"}
+    pkg = importlib.import_module("3dgs_hierarchical_training_b200")
+    pkg.install()
+    import htgs_synthetic as syn
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    cfg, scene, cam, up = syn.make_config(args.workload, device=dev)
+    bg = torch.zeros(3, device=dev)
+
+    def step():
+        fw = refcuda.forward(scene["means3D"], scene["opacities"], cam, bg, 3, shs=scene["shs"], scales=scene["scales"],
+                             rotations=scene["rotations"], want_state=False)
+        refcuda.backward(fw, scene["means3D"], cam, bg, up["dL_dcolor"], up["dL_ddepth"], up["dL_dalpha"], 3, shs=scene["shs"],
+                         scales=scene["scales"], rotations=scene["rotations"])
+        return fw
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        fw = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    # forward-only share
+    e0.record()
+    for _ in range(args.steps):
+        refcuda.forward(scene["means3D"], scene["opacities"], cam, bg, 3, shs=scene["shs"], scales=scene["scales"],
+                        rotations=scene["rotations"], want_state=False)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_fwd = e0.elapsed_time(e1) / args.steps
+    return {"metric": f"fwd+bwd rasterize views/s ({args.workload})", "value": 1e3 / ms, "unit": "views/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "ms_forward_only": ms_fwd,
+            "higher_is_better": True, "impl": "refcuda", "R_instances": fw["R"],
+            "note": "unmodified reference CUDA (oracle/_ref), torch.zeros outputs + 10 zero-filled grad tensors per step as rasterize_points.cu does"}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        out = run_reference(args, rank)
+    elif args.impl == "refcuda":
+        out = run_refcuda(args, rank, local_rank)
+    else:
+        import torch
+        if world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        out = run_ours(args, rank, world, local_rank)
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+    if rank == 0 and out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

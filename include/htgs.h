@@ -135,6 +135,20 @@ size_t htgs_sort_scratch_bytes(int64_t n);
 int htgs_sort_pairs(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* values_in,
                     uint64_t* keys_out, uint32_t* values_out, void* scratch, void* stream);
 
+/* ---- measurement aids (no counterpart in the reference, which has no timers or counters) ----
+ * htgs_profile_enable(1) makes the forward/backward entry points record a CUDA event pair on the
+ * caller's stream around each stage; htgs_profile_read() waits for them, returns the summed
+ * milliseconds and launch counts per stage (order: preprocess, scan, make_keys, sort, tile_ranges,
+ * blend_fwd, zero_acc, blend_bwd, geom_bwd) and clears the log.  Process-wide, not thread-safe.
+ * htgs_blend_stats() re-walks the tile lists of the last forward and writes three counters to
+ * stats3 (device, 3 x uint64): pair tests of the reference's per-pixel loop, blended pairs, pair
+ * tests this library executes after reach-mask culling. */
+#define HTGS_NUM_STAGES 9
+void htgs_profile_enable(int on);
+int htgs_profile_read(double* ms_sum, int* counts, int cap);
+int htgs_blend_stats(int P, int64_t R, int W, int H, const void* geom_buf, const void* binning_buf,
+                     const void* image_buf, unsigned long long* stats3, void* stream);
+
 /* ---- simple-knn ----
  * Replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:15-26,
  * simple_knn.cu:186-222): out[i] = mean of the squared distances from point i

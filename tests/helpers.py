@@ -1,0 +1,92 @@
+"""Shared helpers of the parity tests (not a test module)."""
+import numpy as np
+import torch
+
+import htgs_native as nat
+
+GRAD_NAMES = ["dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales", "dL_drotations"]
+
+# Tolerances of BASELINE.json / SURVEY.md section 8d
+IMAGE_ATOL = 1e-5   # max-abs on colour / depth / alpha (fp32)
+GRAD_RTOL = 1e-4    # ||g - g_ref||_inf / ||g_ref||_inf per tensor
+# The CPU oracle cannot reproduce the GPU's ex2.approx bit for bit (a couple of ulp in G), so a pair
+# that sits on one of the reference's hard thresholds (alpha < 1/255, T*(1-alpha) < 1e-4) can flip.
+# Against the ORACLE only, this fraction of pixels may exceed IMAGE_ATOL (vs the reference CUDA: none).
+ORACLE_PIXEL_OUTLIER_FRAC = 2e-4
+ORACLE_GRAD_RTOL = 5e-3
+
+
+def np_(x):
+    return x.detach().cpu().numpy() if hasattr(x, "detach") else np.asarray(x)
+
+
+def rel_inf(a, b):
+    a, b = np_(a).astype(np.float64), np_(b).astype(np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)) if a.size else 0.0
+
+
+def bits_equal(a, b):
+    a, b = np_(a), np_(b)
+    return a.shape == b.shape and a.tobytes() == b.tobytes()
+
+
+def view_state(geom, binning, img, P, R, W, H):
+    """Typed views of the opaque work buffers through the layout queries of the C ABI."""
+    gl, bl, il = nat.geom_layout(P), nat.binning_layout(R, W, H), nat.image_layout(W, H)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def sl(buf, off, n, dtype):
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        return buf[off:off + nbytes].view(dtype)
+
+    st = dict(means2D=sl(geom, gl["means2D"], 2 * P, torch.float32).view(P, 2),
+              conic_opacity=sl(geom, gl["conic_opacity"], 4 * P, torch.float32).view(P, 4),
+              feat=sl(geom, gl["feat"], 4 * P, torch.float32).view(P, 4),
+              clamped=sl(geom, gl["clamped"], P, torch.uint8),
+              tiles_touched=sl(geom, gl["tiles_touched"], P, torch.int32),
+              point_offsets=sl(geom, gl["point_offsets"], P, torch.int32),
+              ranges=sl(img, il["ranges"], 2 * tiles, torch.int32).view(tiles, 2),
+              n_contrib=sl(img, il["n_contrib"], W * H, torch.int32).view(H, W))
+    if R > 0:
+        st["keys"] = sl(binning, bl["keys_sorted"], R, torch.int64)
+        st["point_list"] = sl(binning, bl["values_sorted"], R, torch.int32)
+    return st
+
+
+def run_ours(scene, cam, up, bg, deg=3, colors_precomp=None, cov3D_precomp=None, scale_modifier=1.0, debug=False):
+    """Forward + backward through the mirror of the pybind entry points (`_C`), returning outputs,
+    typed state views and the 8 gradients."""
+    from diff_gaussian_rasterization import _C
+    empty = torch.Tensor([])
+    shs = empty if colors_precomp is not None else scene["shs"]
+    colors = colors_precomp if colors_precomp is not None else empty
+    scales = empty if cov3D_precomp is not None else scene["scales"]
+    rots = empty if cov3D_precomp is not None else scene["rotations"]
+    cov = cov3D_precomp if cov3D_precomp is not None else empty
+    P, W, H = scene["means3D"].shape[0], cam["W"], cam["H"]
+    R, color, depth, alpha, radii, geom, binning, img = _C.rasterize_gaussians(
+        bg, scene["means3D"], colors, scene["opacities"], scales, rots, scale_modifier, cov, cam["viewmatrix"],
+        cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], H, W, shs, deg, cam["campos"], False, debug)
+    grads = _C.rasterize_gaussians_backward(
+        bg, scene["means3D"], radii, colors, scales, rots, scale_modifier, cov, cam["viewmatrix"], cam["projmatrix"],
+        cam["tanfovx"], cam["tanfovy"], up["dL_dcolor"], up["dL_ddepth"], up["dL_dalpha"], shs, deg, cam["campos"], geom, R,
+        binning, img, alpha, debug)
+    torch.cuda.synchronize()
+    out = dict(R=R, color=color, depth=depth, alpha=alpha, radii=radii)
+    out.update(view_state(geom, binning, img, P, R, W, H) if P > 0 else {})
+    out["grads"] = dict(zip(GRAD_NAMES, grads))
+    return out
+
+
+def cov3d_of(scene):
+    """Sigma = R S S^T R^T packed as the 6 upper-triangular entries, like
+    HTGaussianModel.get_covariance (scene/gaussian_model_ht.py:49-56); float64 maths, fp32 result."""
+    q = scene["rotations"].double()
+    s = scene["scales"].double()
+    r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rm = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                      2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                      2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], 1).view(-1, 3, 3)
+    L = Rm * s[:, None, :]
+    S = L @ L.transpose(1, 2)
+    return torch.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1).float().contiguous()

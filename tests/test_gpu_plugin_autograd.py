@@ -1,0 +1,96 @@
+"""The autograd contract of the drop-in plugin: 4-tuple, gradient slots,
+retain_grad on the dummy means2D, in-place edits of the returned depth/colour, zero-materialised
+grads for unused outputs, accumulation over several views (what view-parallel training relies on)."""
+import numpy as np
+import pytest
+import torch
+
+import htgs_synthetic as syn
+from helpers import GRAD_RTOL, np_, rel_inf
+from oracle import golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(cfgname="small"):
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    dev = torch.device("cuda:0")
+    cfg, scene, cam, up = syn.make_config(cfgname, device=dev)
+    bg = torch.zeros(3, device=dev)
+    rs = GaussianRasterizationSettings(image_height=cfg["H"], image_width=cfg["W"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+                                       bg=bg, scale_modifier=1.0, viewmatrix=cam["viewmatrix"], projmatrix=cam["projmatrix"],
+                                       sh_degree=3, campos=cam["campos"], prefiltered=False, debug=False)
+    return cfg, scene, cam, up, bg, GaussianRasterizer(raster_settings=rs)
+
+
+def test_render_like_cf3dgs_render():
+    """Mimics CF3DGS_Render.render (scene/gaussian_model_ht.py:775-908) and train_step's use of it."""
+    cfg, scene, cam, up, bg, rast = _setup()
+    xyz = scene["means3D"].clone().requires_grad_(True)
+    raw_op = torch.logit(scene["opacities"].clamp(1e-4, 1 - 1e-4)).requires_grad_(True)
+    raw_sc = torch.log(scene["scales"]).requires_grad_(True)
+    raw_rot = (scene["rotations"] * 1.7).requires_grad_(True)
+    f_dc = scene["shs"][:, :1].clone().requires_grad_(True)
+    f_rest = scene["shs"][:, 1:].clone().requires_grad_(True)
+    screenspace_points = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device="cuda") + 0
+    screenspace_points.retain_grad()
+    out = rast(means3D=xyz, means2D=screenspace_points, shs=torch.cat((f_dc, f_rest), dim=1), colors_precomp=None,
+               opacities=torch.sigmoid(raw_op), scales=torch.exp(raw_sc), rotations=torch.nn.functional.normalize(raw_rot),
+               cov3D_precomp=None)
+    assert len(out) == 4
+    rendered_image, radii, depth, alpha = out
+    assert rendered_image.shape == (3, cfg["H"], cfg["W"]) and depth.shape == alpha.shape == (1, cfg["H"], cfg["W"])
+    assert radii.dtype == torch.int32 and not radii.requires_grad
+    image = rendered_image.clamp(0, 1)
+    depth[depth < 0.5] = 0.5  # in-place edit of the plugin's output (trainer/ht3dgs_trainer.py:1292)
+    loss = (image * up["dL_dcolor"]).sum() + (depth * up["dL_ddepth"]).sum()  # alpha unused -> zero grad materialised
+    loss.backward()
+    for t in (xyz, raw_op, raw_sc, raw_rot, f_dc, f_rest):
+        assert t.grad is not None and bool(torch.isfinite(t.grad).all())
+    vsp = screenspace_points.grad
+    assert vsp.shape == xyz.shape and not vsp[:, 2].any()          # z slot never written
+    vis = radii > 0
+    assert not vsp[~vis].any() and bool(vsp[vis].abs().sum() > 0)  # densification stat source
+    assert bool(torch.norm(vsp[vis, :2], dim=-1).isfinite().all())
+
+
+def test_gradient_accumulates_over_views_and_matches_oracle():
+    """Two cameras, one backward each, parameter grads accumulate -- the per-GPU half of view-parallel training."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    dev = torch.device("cuda:0")
+    cfg, scene, _, up = syn.make_config("small", device=dev)
+    bg = torch.tensor([0.1, 0.3, 0.2], device=dev)
+    params = {k: v.clone().requires_grad_(True) for k, v in scene.items()}
+    total = {k: 0.0 for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations")}
+    for yaw in (-4.0, 5.0):
+        cam = syn.make_camera(cfg["W"], cfg["H"], yaw_deg=yaw, device=dev)
+        rs = GaussianRasterizationSettings(cfg["H"], cfg["W"], cam["tanfovx"], cam["tanfovy"], bg, 1.0, cam["viewmatrix"],
+                                           cam["projmatrix"], 3, cam["campos"], False, False)
+        color, radii, depth, alpha = GaussianRasterizer(rs)(
+            means3D=params["means3D"], means2D=torch.zeros_like(params["means3D"], requires_grad=True),
+            opacities=params["opacities"], shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        torch.autograd.backward((color, depth, alpha), (up["dL_dcolor"], up["dL_ddepth"], up["dL_dalpha"]))
+        o = golden.forward(scene["means3D"], scene["opacities"], cam, bg, 3, shs=scene["shs"], scales=scene["scales"],
+                           rotations=scene["rotations"])
+        og = golden.backward(o, up["dL_dcolor"], up["dL_ddepth"], up["dL_dalpha"])
+        for k in total:
+            total[k] = total[k] + og[k].astype(np.float64)
+    got = dict(dL_dmeans3D=params["means3D"].grad, dL_dsh=params["shs"].grad, dL_dopacity=params["opacities"].grad,
+               dL_dscales=params["scales"].grad, dL_drotations=params["rotations"].grad)
+    for k, v in got.items():
+        assert rel_inf(v, total[k].reshape(np_(v).shape)) <= 5e-3, k
+
+
+def test_forward_only_no_grad_and_colors_precomp_grad_slot():
+    cfg, scene, cam, up, bg, rast = _setup("tiny")
+    with torch.no_grad():
+        out = rast(means3D=scene["means3D"], means2D=torch.zeros_like(scene["means3D"]), opacities=scene["opacities"],
+                   shs=scene["shs"], scales=scene["scales"], rotations=scene["rotations"])
+    assert not out[0].requires_grad
+    colors = torch.rand(cfg["P"], 3, device="cuda").requires_grad_(True)
+    color, radii, depth, alpha = rast(means3D=scene["means3D"], means2D=torch.zeros_like(scene["means3D"]),
+                                      opacities=scene["opacities"], colors_precomp=colors, scales=scene["scales"],
+                                      rotations=scene["rotations"])
+    color.sum().backward()
+    assert colors.grad is not None and colors.grad.shape == colors.shape and bool((colors.grad >= 0).all())
+    assert not colors.grad[radii == 0].any()
