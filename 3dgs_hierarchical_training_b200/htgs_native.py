@@ -34,6 +34,7 @@ _SIGNATURES = {
     "htgs_mark_visible": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_sort_scratch_bytes": (c_size_t, [c_int64]),
     "htgs_sort_pairs": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_sort_pairs_static": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_profile_enable": (None, [c_int]),
     "htgs_profile_read": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int), c_int]),
     "htgs_blend_stats": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -43,6 +44,7 @@ _SIGNATURES = {
 
 EXPORTS = tuple(_SIGNATURES)
 ABI_VERSION = 1
+SORT_STATIC_MAX_PAIRS = 1 << 20  # HTGS_SORT_STATIC_MAX_PAIRS
 
 GEOM_FIELDS = ("means2D", "conic_opacity", "feat", "clamped", "tiles_touched", "point_offsets", "block_sums", "num_rendered")
 BIN_FIELDS = ("keys_sorted", "values_sorted", "keys_alt", "values_alt", "sort_scratch")

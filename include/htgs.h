@@ -135,6 +135,25 @@ size_t htgs_sort_scratch_bytes(int64_t n);
 int htgs_sort_pairs(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* values_in,
                     uint64_t* keys_out, uint32_t* values_out, void* scratch, void* stream);
 
+/* htgs_sort_pairs_static has no counterpart in the reference.  It is htgs_sort_pairs for callers
+ * that may not allocate device memory at all -- a plugin living inside a host application's
+ * pre-reserved arena, a serving process with a fixed and accounted pool, a latency-critical loop
+ * that cannot afford the device-wide synchronisation of cudaMalloc/cudaFree.  They still pass
+ * their own input and output arrays, but the scratch comes from a fixed array inside the library
+ * image (HTGS_SORT_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until exit), so:
+ *   - at most HTGS_SORT_STATIC_MAX_PAIRS pairs; a larger n is refused with an error message;
+ *   - nothing is allocated or freed, by this call or by anything it uses;
+ *   - all calls on a device share that one array.  Each call clears the part it needs first, so
+ *     what the previous call left behind is harmless, but calls whose GPU work overlaps (other
+ *     streams, other host threads) corrupt each other: keep them ordered;
+ *   - the first call on each device looks up the array's device address; issue that first call
+ *     outside any stream capture.
+ * Same contract as htgs_sort_pairs otherwise (stable, key bits [0,end_bit), inputs clobbered). */
+#define HTGS_SORT_STATIC_MAX_PAIRS (1LL << 20)
+#define HTGS_SORT_STATIC_SCRATCH_BYTES 2105856
+int htgs_sort_pairs_static(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* values_in,
+                           uint64_t* keys_out, uint32_t* values_out, void* stream);
+
 /* ---- measurement aids (no counterpart in the reference, which has no timers or counters) ----
  * htgs_profile_enable(1) makes the forward/backward entry points record a CUDA event pair on the
  * caller's stream around each stage; htgs_profile_read() waits for them, returns the summed
