@@ -1,0 +1,56 @@
+"""View-parallel plumbing: one process per GPU, full Gaussian replica on every
+rank, each rank rasterizes its own cameras, one all-reduce of the flat parameter gradient per step.
+
+The reference has no distributed code at all; this is the only multi-GPU shape its hot path admits
+(a single image is never split).  torch.distributed (NCCL on GPUs, gloo in the CPU tests) does the
+transport; nothing here touches the rasterizer.
+"""
+import torch
+import torch.distributed as dist
+
+# parameter order and floats per Gaussian of the flat buffer: xyz 3, SH 48 (f_dc 3 + f_rest 45),
+# opacity 1, scaling 3, rotation 4 = 59  (layout of the optimizer groups, scene/gaussian_model_ht.py:275-287)
+PARAM_ORDER = ("means3D", "shs", "opacities", "scales", "rotations")
+FLOATS_PER_GAUSSIAN = 59
+
+
+def shard_views(num_views, rank, world):
+    """Contiguous, balanced split of view indices: rank r gets views [lo, hi)."""
+    base, extra = divmod(num_views, world)
+    lo = rank * base + min(rank, extra)
+    return range(lo, lo + base + (1 if rank < extra else 0))
+
+
+class FlatGradReducer:
+    """Packs the five parameter gradients into one contiguous buffer, all-reduces it once (sum),
+    and hands the reduced views back -- one collective of 236 B/Gaussian instead of five."""
+
+    def __init__(self, P, device, dtype=torch.float32):
+        self.P = P
+        self.flat = torch.zeros(P * FLOATS_PER_GAUSSIAN, device=device, dtype=dtype)
+        self.slices = {}
+        o = 0
+        for name, per in zip(PARAM_ORDER, (3, 48, 1, 3, 4)):
+            self.slices[name] = (o, o + P * per)
+            o += P * per
+        assert o == self.flat.numel()
+
+    def pack(self, grads):
+        for name in PARAM_ORDER:
+            lo, hi = self.slices[name]
+            g = grads[name]
+            if g is None:
+                self.flat[lo:hi].zero_()
+            else:
+                self.flat[lo:hi].copy_(g.reshape(-1))
+        return self.flat
+
+    def all_reduce(self, average=False):
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+            if average:
+                self.flat.div_(dist.get_world_size())
+        return self.flat
+
+    def unpack(self, like):
+        return {name: self.flat[lo:hi].view_as(like[name]) for name, (lo, hi) in self.slices.items()}

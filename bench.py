@@ -29,7 +29,6 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GPU_LAUNCHES_FWD = 12  # preprocess, scan, make_keys, hist, scan_hist, 6 x onesweep (config3: 45 key bits), ranges... see below
 
 
 def parse():
@@ -128,7 +127,8 @@ def run_ours(args, rank, world, local_rank):
     bg = torch.zeros(3, device=dev)  # HT renderers use a black background (trainer/ht3dgs_trainer.py:47-53)
     up_d = {k: v.to(dev) for k, v in up.items()}
     cam_d = {k: (v.to(dev) if hasattr(v, "to") else v) for k, v in cam_h.items()}
-    flat = torch.zeros(P * 59, device=dev) if world > 1 else None
+    import htgs_dist
+    reducer = htgs_dist.FlatGradReducer(P, dev) if world > 1 else None
 
     def settings(cam):
         return dgr.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
@@ -145,12 +145,8 @@ def run_ours(args, rank, world, local_rank):
                                           shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
         torch.autograd.backward((color, depth, alpha), (upg["dL_dcolor"], upg["dL_ddepth"], upg["dL_dalpha"]))
         if world > 1:
-            o = 0
-            for k in ("means3D", "shs", "opacities", "scales", "rotations"):
-                g = params[k].grad.reshape(-1)
-                flat[o:o + g.numel()].copy_(g)
-                o += g.numel()
-            dist.all_reduce(flat)
+            reducer.pack({k: params[k].grad for k in htgs_dist.PARAM_ORDER})
+            reducer.all_reduce()
         return color, radii
 
     def barrier():
@@ -198,9 +194,9 @@ def run_ours(args, rank, world, local_rank):
             for k, v in host_cam.items():
                 cam[k] = v.to(dev, non_blocking=True)
             color, radii = step(cam, upg)
-            s = (color.double().sum() + params["opacities"].grad.double().sum()).reshape(1)
+            s = (color.detach().double().sum() + params["opacities"].grad.double().sum()).reshape(1)
             result.copy_(s, non_blocking=False)  # device->host read of the step's scalar result
-            return float(result[0])
+            return float(result[0].detach())
 
         for _ in range(3):
             e2e_step()
@@ -378,6 +374,11 @@ def run_refcuda(args, rank, local_rank):
 
 def main():
     args = parse()
+    # Exactly ONE line may reach stdout (the JSON).  Libraries (NCCL prints its version banner on
+    # stdout) are pointed at stderr for the duration of the run; the JSON goes to the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
@@ -396,8 +397,10 @@ def main():
         if world > 1:
             import torch.distributed as dist
             dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     if rank == 0 and out is not None:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
 
 
 if __name__ == "__main__":
