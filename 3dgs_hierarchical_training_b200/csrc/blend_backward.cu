@@ -16,6 +16,15 @@
 // The 8x4 reach masks of blend_common.cuh skip Gaussians that cannot touch a
 // warp's pixels, and whole batches behind the tile's last contributor.
 //
+// Instruction economy (the kernel is FP32-issue bound): a lane does not form the five geometric
+// gradients itself.  With w = G * dL/dalpha it only accumulates the moments  w, w*dx, w*dy,
+// w*dx*dx, w*dx*dy, w*dy*dy ; the conic/opacity factors, which are per-Gaussian constants, are
+// applied once per (tile, Gaussian) when the batch is flushed.  Likewise the per-channel
+// "accumulated colour behind me" recurrences of backward.cu:547-567 collapse into one scalar
+// recurrence of their dot product with the pixel's upstream gradient (they only ever enter
+// dL/dalpha through that dot product).  Same sums, re-associated; thresholds, alpha and the
+// T = T/(1-alpha) chain are untouched.
+//
 // Accumulator layout gacc[P][12] (zeroed by the caller):
 //   [0..3] dL/dmean2D.x, .y, dL/dopacity, dL/ddepth   [4..6] dL/dconic x,y,w
 //   [8..10] dL/dcolour rgb                             [7],[11] unused
@@ -26,7 +35,7 @@ namespace htgs {
 constexpr int BWD_BATCH = 128;
 constexpr int BWD_NV = 10;
 
-// value order inside the kernel: 0 mean.x 1 mean.y 2 opacity 3 depth 4..6 conic x,y,w 7..9 rgb
+// value order inside the kernel: 0 w 1 w*dx 2 w*dy 3 depth-grad 4..6 w*dx*dx, w*dx*dy, w*dy*dy 7..9 rgb-grad
 struct Reduce10 {
     bool b4, b3, b2, b1, writer;
     int id;
@@ -76,9 +85,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth_pix,
                       const float* __restrict__ dL_dalpha_pix, float* __restrict__ gacc) {
     __shared__ float s_stage[BLEND_WARPS][BWD_BATCH][BWD_NV];  // 40 KB
-    __shared__ float4 s_co[BWD_BATCH];
-    __shared__ float4 s_feat[BWD_BATCH];
-    __shared__ float2 s_xy[BWD_BATCH];
+    __shared__ StagedGaussian s_g[BWD_BATCH];
     __shared__ uint32_t s_id[BWD_BATCH];
     __shared__ uint8_t s_mask[BWD_BATCH];
     __shared__ uint32_t s_warp_last[BLEND_WARPS];
@@ -99,18 +106,20 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const float T_final = inside ? 1.0f - alphas[pix] : 0.f;
     float T = T_final;
     const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
-    float dLdp0 = 0.f, dLdp1 = 0.f, dLdp2 = 0.f, dLdd = 0.f, dLda = 0.f;
+    float d0 = 0.f, d1 = 0.f, d2 = 0.f, dd = 0.f, da = 0.f;
     if (inside) {
-        dLdp0 = dL_dpix[pix];
-        dLdp1 = dL_dpix[plane + pix];
-        dLdp2 = dL_dpix[2 * plane + pix];
-        dLdd = dL_ddepth_pix[pix];
-        dLda = dL_dalpha_pix[pix];
+        d0 = dL_dpix[pix];
+        d1 = dL_dpix[plane + pix];
+        d2 = dL_dpix[2 * plane + pix];
+        dd = dL_ddepth_pix[pix];
+        da = dL_dalpha_pix[pix];
     }
-    const float bg_dot_dpixel = bg[0] * dLdp0 + bg[1] * dLdp1 + bg[2] * dLdp2;  // backward.cu:575-577
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, accd = 0.f, acca = 0.f;
-    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:490-491
+    // -(T_final * bg . dL/dpixel): numerator of the background term, backward.cu:575-578
+    const float bg_k = -T_final * (bg[0] * d0 + bg[1] * d1 + bg[2] * d2);
+    const bool warp_has_bg = __any_sync(0xffffffffu, bg_k != 0.f);
+    // A = sum_ch accum_rec[ch]*dL/dch (colour, depth, alpha channels); Cprev = the same dot product
+    // for the previously visited Gaussian's own colour/depth/1
+    float A = 0.f, Cprev = 0.f, last_alpha = 0.f;
 
     uint32_t wl = last_contributor;
 #pragma unroll
@@ -124,6 +133,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
     Reduce10 red;
     red.init(lane);
+    const uint32_t sg_base = smem_u32(s_g);
+    const uint32_t stage_base = smem_u32(&s_stage[warp][0][0]) + (uint32_t)red.id * 4u;
 
     for (int base = 0; base < n; base += BWD_BATCH) {
         const int cnt = min(BWD_BATCH, n - base);
@@ -136,9 +147,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const float2 xy = means2D[g];
             const float4 co = conic_opacity[g];
             s_id[tid] = g;
-            s_xy[tid] = xy;
-            s_co[tid] = co;
-            s_feat[tid] = feat[g];
+            stage_gaussian(&s_g[tid], xy, co, feat[g]);
             s_mask[tid] = (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
         }
         __syncthreads();
@@ -146,62 +155,52 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const int j = c0 + lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1) && (uint32_t)(top - j) < warp_last;
             uint32_t m = __ballot_sync(0xffffffffu, mine);
+            const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
+            const uint32_t chunk_stage = stage_base + (uint32_t)c0 * (BWD_NV * 4u);
+            const uint32_t chunk_top = (uint32_t)(top - c0);
             while (m) {
-                const int idx = c0 + __ffs(m) - 1;
+                const int b = __ffs(m) - 1;
                 m &= m - 1;
-                const uint32_t pos0 = (uint32_t)(top - idx);  // == `contributor` after the decrement (backward.cu:517)
+                const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
+                const float4 q0 = lds128(a);       // mean.xy, conic.xy
+                const float4 q1 = lds128(a + 16);  // conic.z, opacity, r, g
+                const float dx = SB(q0.x, pxf), dy = SB(q0.y, pyf);
+                const float power = pair_power(dx, dy, q0.z, q0.w, q1.x);
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, MU(q1.y, G));
+                // `contributor` after its decrement is chunk_top - b (backward.cu:517-519)
+                const bool live = (chunk_top - (uint32_t)b) < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 float v[BWD_NV];
 #pragma unroll
                 for (int k = 0; k < BWD_NV; k++) v[k] = 0.f;
-                bool contributed = false;
-                if (pos0 < last_contributor) {
-                    const float2 xy = s_xy[idx];
-                    const float4 co = s_co[idx];
-                    const float dx = SB(xy.x, pxf), dy = SB(xy.y, pyf);
-                    const float power = pair_power(dx, dy, co.x, co.y, co.z);
-                    if (!(power > 0.0f)) {
-                        const float G = expf(power);
-                        const float alpha = fminf(0.99f, MU(co.w, G));
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            contributed = true;
-                            const float4 f = s_feat[idx];
-                            T = __fdiv_rn(T, SB(1.f, alpha));
-                            const float dchannel_dcolor = alpha * T;
-                            const float one_m_la = 1.f - last_alpha;
-                            float dL_dopa;
-                            acc0 = last_alpha * lc0 + one_m_la * acc0; lc0 = f.x;
-                            dL_dopa = (f.x - acc0) * dLdp0;
-                            acc1 = last_alpha * lc1 + one_m_la * acc1; lc1 = f.y;
-                            dL_dopa += (f.y - acc1) * dLdp1;
-                            acc2 = last_alpha * lc2 + one_m_la * acc2; lc2 = f.z;
-                            dL_dopa += (f.z - acc2) * dLdp2;
-                            v[7] = dchannel_dcolor * dLdp0;
-                            v[8] = dchannel_dcolor * dLdp1;
-                            v[9] = dchannel_dcolor * dLdp2;
-                            accd = last_alpha * ld + one_m_la * accd; ld = f.w;
-                            dL_dopa += (f.w - accd) * dLdd;
-                            v[3] = dchannel_dcolor * dLdd;
-                            acca = last_alpha + one_m_la * acca;
-                            dL_dopa += (1.f - acca) * dLda;
-                            dL_dopa *= T;
-                            last_alpha = alpha;
-                            dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-                            const float dL_dG = co.w * dL_dopa;
-                            const float gdx = G * dx, gdy = G * dy;
-                            const float dG_ddelx = -gdx * co.x - gdy * co.y;
-                            const float dG_ddely = -gdy * co.z - gdx * co.y;
-                            v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                            v[1] = dL_dG * dG_ddely * ddely_dy;
-                            v[4] = -0.5f * gdx * dx * dL_dG;
-                            v[5] = -0.5f * gdx * dy * dL_dG;
-                            v[6] = -0.5f * gdy * dy * dL_dG;
-                            v[2] = G * dL_dopa;
-                        }
-                    }
+                if (live) {
+                    const float2 q2 = lds64(a + 32);  // b, depth
+                    const float one_m_a = SB(1.f, alpha);
+                    T = __fdiv_rn(T, one_m_a);                                   // backward.cu:534
+                    const float aT = alpha * T;
+                    const float Cd = fmaf(q2.y, dd, fmaf(q2.x, d2, fmaf(q1.w, d1, fmaf(q1.z, d0, da))));
+                    A = fmaf(last_alpha, Cprev, (1.f - last_alpha) * A);
+                    Cprev = Cd;
+                    last_alpha = alpha;
+                    float dL_dopa = (Cd - A) * T;
+                    if (warp_has_bg) dL_dopa += __fdividef(bg_k, one_m_a);
+                    const float w = G * dL_dopa;
+                    const float wdx = w * dx, wdy = w * dy;
+                    v[0] = w;          // -> dL/dopacity, and scaled by opacity the common factor below
+                    v[1] = wdx;        // first moments  -> dL/dmean2D
+                    v[2] = wdy;
+                    v[3] = aT * dd;    // dL/ddepth
+                    v[4] = wdx * dx;   // second moments -> dL/dconic
+                    v[5] = wdx * dy;
+                    v[6] = wdy * dy;
+                    v[7] = aT * d0;    // dL/dcolour
+                    v[8] = aT * d1;
+                    v[9] = aT * d2;
                 }
                 float total = 0.f;
-                if (__any_sync(0xffffffffu, contributed)) total = red.run(v);
-                if (red.writer) s_stage[warp][idx][red.id] = total;
+                if (__any_sync(0xffffffffu, live)) total = red.run(v);
+                if (red.writer)
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(chunk_stage + (uint32_t)b * (BWD_NV * 4u)), "f"(total) : "memory");
             }
         }
         __syncthreads();
@@ -218,9 +217,17 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     for (int k = 0; k < BWD_NV; k++) s[k] += s_stage[w][tid][k];
                 }
             }
+            // moments -> gradients (backward.cu:582-598), per-Gaussian constants applied once here
+            const float4 q0 = s_g[tid].q0;
+            const float4 q1 = s_g[tid].q1;
+            const float cx = q0.z, cy = q0.w, cz = q1.x, op = q1.y;
+            const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:490-491
+            const float gmx = -op * (cx * s[1] + cy * s[2]) * ddelx_dx;
+            const float gmy = -op * (cz * s[2] + cy * s[1]) * ddely_dy;
+            const float gcx = -0.5f * op * s[4], gcy = -0.5f * op * s[5], gcw = -0.5f * op * s[6];
             float4* dst = reinterpret_cast<float4*>(gacc + (size_t)s_id[tid] * 12);
-            if (s[0] != 0.f || s[1] != 0.f || s[2] != 0.f || s[3] != 0.f) atomicAdd(dst, make_float4(s[0], s[1], s[2], s[3]));
-            if (s[4] != 0.f || s[5] != 0.f || s[6] != 0.f) atomicAdd(dst + 1, make_float4(s[4], s[5], s[6], 0.f));
+            if (s[0] != 0.f || s[1] != 0.f || s[2] != 0.f || s[3] != 0.f) atomicAdd(dst, make_float4(gmx, gmy, s[0], s[3]));
+            if (s[4] != 0.f || s[5] != 0.f || s[6] != 0.f) atomicAdd(dst + 1, make_float4(gcx, gcy, gcw, 0.f));
             if (s[7] != 0.f || s[8] != 0.f || s[9] != 0.f) atomicAdd(dst + 2, make_float4(s[7], s[8], s[9], 0.f));
         }
     }

@@ -9,6 +9,12 @@
 // hit the reference's `alpha < 1/255` rejection (forward.cu:348), so the set and
 // order of blended contributions per pixel -- and hence every output bit -- is
 // unchanged.
+//
+// Both kernels are FP32-issue bound (ncu: issue slots 73-80% busy), so the inner
+// loops are written for instruction count: one 48-byte shared-memory record per
+// staged Gaussian read with two (three when blending) 128-bit loads from an
+// address formed by a single multiply-add, and one combined predicate instead of
+// a branch per rejection test.
 #pragma once
 #include "gs_math.cuh"
 
@@ -20,20 +26,43 @@ constexpr int BLEND_WARPS = 8;
 __device__ __forceinline__ int warp_block_x(int w) { return (w & 1) * 8; }
 __device__ __forceinline__ int warp_block_y(int w) { return (w >> 1) * 4; }
 
+// One staged Gaussian in shared memory (48 B, 16-byte aligned):
+//   q0 = (mean.x, mean.y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, depth, -, -)
+struct __align__(16) StagedGaussian {
+    float4 q0, q1, q2;
+};
+constexpr int STAGED_BYTES = 48;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ float2 lds64(uint32_t a) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void stage_gaussian(StagedGaussian* dst, float2 xy, float4 co, float4 f) {
+    dst->q0 = make_float4(xy.x, xy.y, co.x, co.y);
+    dst->q1 = make_float4(co.z, co.w, f.x, f.y);
+    dst->q2 = make_float4(f.z, f.w, 0.f, 0.f);
+}
+
 // Minimum over the rectangle dx in [dxl,dxh], dy in [dyl,dyh] of the convex
 // quadratic q = 0.5*(A dx^2 + C dy^2) + B dx dy  ( = -power ).
-__device__ __forceinline__ float quad_min_over_rect(float A, float B, float C, float dxl, float dxh, float dyl,
-                                                    float dyh) {
+__device__ __forceinline__ float quad_min_over_rect(float A, float B, float C, float nBiC, float nBiA, float dxl,
+                                                    float dxh, float dyl, float dyh) {
     if (dxl <= 0.f && dxh >= 0.f && dyl <= 0.f && dyh >= 0.f) return 0.f;
     float best = 3.0e38f;
-    const float invC = 1.f / C, invA = 1.f / A;
 #pragma unroll
     for (int s = 0; s < 2; s++) {
         const float ex = s ? dxh : dxl;  // vertical edges dx = ex
-        float dy = fminf(dyh, fmaxf(dyl, -B * ex * invC));
+        const float dy = fminf(dyh, fmaxf(dyl, nBiC * ex));
         best = fminf(best, 0.5f * (A * ex * ex + C * dy * dy) + B * ex * dy);
         const float ey = s ? dyh : dyl;  // horizontal edges dy = ey
-        float dx = fminf(dxh, fmaxf(dxl, -B * ey * invA));
+        const float dx = fminf(dxh, fmaxf(dxl, nBiA * ey));
         best = fminf(best, 0.5f * (A * dx * dx + C * ey * ey) + B * dx * ey);
     }
     return best;
@@ -52,13 +81,14 @@ __device__ __forceinline__ uint32_t block_reach_mask(float2 xy, float4 co, int t
         return 0xffu;
     // contributes only if -power <= ln(255*o)
     const float thr = __logf(255.0f * o) * 1.0001f + 1e-3f;
+    const float nBiC = -B / C, nBiA = -B / A;
     uint32_t m = 0;
 #pragma unroll
     for (int w = 0; w < BLEND_WARPS; w++) {
         const float x0 = (float)(tile_x0 + warp_block_x(w)), y0 = (float)(tile_y0 + warp_block_y(w));
         const float dxl = xy.x - (x0 + 7.f), dxh = xy.x - x0;
         const float dyl = xy.y - (y0 + 3.f), dyh = xy.y - y0;
-        const float q = quad_min_over_rect(A, B, C, dxl, dxh, dyl, dyh);
+        const float q = quad_min_over_rect(A, B, C, nBiC, nBiA, dxl, dxh, dyl, dyh);
         const float mx = fmaxf(fabsf(dxl), fabsf(dxh)), my = fmaxf(fabsf(dyl), fabsf(dyh));
         const float slack = 4e-6f * (A * mx * mx + C * my * my + fabsf(B) * mx * my);
         if (q <= thr + slack) m |= 1u << w;

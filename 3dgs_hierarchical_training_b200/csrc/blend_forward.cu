@@ -1,8 +1,8 @@
 // K4: front-to-back alpha blend of one 16x16 tile per CTA.
 // Replaces FORWARD::render / renderCUDA (cuda_rasterizer/forward.cu:261-381).
 //
-// Bound: FP32 issue (about 20 FP32-pipe instructions + 1 MUFU per tested
-// pixel/Gaussian pair); the lever is testing fewer pairs.  Gaussians are staged
+// Bound: FP32 issue (ncu r01: issue slots 80% busy, DRAM 1.5%); the levers are testing
+// fewer pairs and spending fewer instructions per test.  Gaussians are staged
 // in shared memory in batches of 256 together with colour+depth (the reference
 // re-fetches those from global memory per blended pair, forward.cu:359-361) and
 // an 8-bit reach mask (blend_common.cuh); each warp walks only the Gaussians
@@ -26,9 +26,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const float4* __restrict__ feat, const float* __restrict__ bg, float* __restrict__ out_color,
                      float* __restrict__ out_depth, float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
                      unsigned long long* __restrict__ stats) {
-    __shared__ float4 s_co[FWD_BATCH];
-    __shared__ float4 s_feat[FWD_BATCH];
-    __shared__ float2 s_xy[FWD_BATCH];
+    __shared__ StagedGaussian s_g[FWD_BATCH];
     __shared__ uint8_t s_mask[FWD_BATCH];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -37,10 +35,11 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     const int py = tile_y0 + warp_block_y(warp) + (lane >> 3);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
-    bool done = !inside;
+    int done = inside ? 0 : 1;
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const int n = (int)(range.y - range.x);
+    const uint32_t sg_base = smem_u32(s_g);
 
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, dsum = 0.f;
     uint32_t last_contributor = 0;
@@ -54,9 +53,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             const uint32_t g = point_list[range.x + base + tid];
             const float2 xy = means2D[g];
             const float4 co = conic_opacity[g];
-            s_xy[tid] = xy;
-            s_co[tid] = co;
-            s_feat[tid] = feat[g];
+            stage_gaussian(&s_g[tid], xy, co, feat[g]);
             s_mask[tid] = (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
         }
         __syncthreads();
@@ -65,33 +62,37 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             const int j = c0 + lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1);
             uint32_t m = __ballot_sync(0xffffffffu, mine);
+            const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
+            const uint32_t chunk_pos = (uint32_t)(base + c0 + 1);
             while (m) {
-                const int idx = c0 + __ffs(m) - 1;
+                const int b = __ffs(m) - 1;
                 m &= m - 1;
-                if (done) continue;
-                if (STATS) st_tested++;
-                const float2 xy = s_xy[idx];
-                const float4 co = s_co[idx];
-                const float dx = SB(xy.x, pxf), dy = SB(xy.y, pyf);
-                const float power = pair_power(dx, dy, co.x, co.y, co.z);
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, MU(co.w, expf(power)));
-                if (alpha < 1.0f / 255.0f) continue;
+                const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
+                const float4 q0 = lds128(a);       // mean.xy, conic.xy
+                const float4 q1 = lds128(a + 16);  // conic.z, opacity, r, g
+                const float dx = SB(q0.x, pxf), dy = SB(q0.y, pyf);
+                const float power = pair_power(dx, dy, q0.z, q0.w, q1.x);
+                const float alpha = fminf(0.99f, MU(q1.y, expf(power)));
                 const float test_T = MU(T, SB(1.0f, alpha));
-                if (test_T < 0.0001f) {
-                    done = true;
-                    if (STATS) st_done_pos = (uint32_t)(base + idx + 1);
-                    continue;
+                // the reference's three rejections (forward.cu:340-355) as one predicate chain
+                const bool live = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (STATS) st_tested += done ? 0u : 1u;
+                const bool kill = live && (test_T < 0.0001f);
+                if (kill) {
+                    done = 1;
+                    if (STATS) st_done_pos = chunk_pos + (uint32_t)b;
                 }
-                const float4 f = s_feat[idx];
-                C0 = FM(T, MU(alpha, f.x), C0);
-                C1 = FM(T, MU(alpha, f.y), C1);
-                C2 = FM(T, MU(alpha, f.z), C2);
-                wsum = FM(T, alpha, wsum);
-                dsum = FM(T, MU(alpha, f.w), dsum);
-                T = test_T;
-                last_contributor = (uint32_t)(base + idx + 1);
-                if (STATS) st_blended++;
+                if (live && !kill) {
+                    const float2 q2 = lds64(a + 32);  // b, depth
+                    C0 = FM(T, MU(alpha, q1.z), C0);
+                    C1 = FM(T, MU(alpha, q1.w), C1);
+                    C2 = FM(T, MU(alpha, q2.x), C2);
+                    wsum = FM(T, alpha, wsum);
+                    dsum = FM(T, MU(alpha, q2.y), dsum);
+                    T = test_T;
+                    last_contributor = chunk_pos + (uint32_t)b;
+                    if (STATS) st_blended++;
+                }
             }
             if (__all_sync(0xffffffffu, done)) break;
         }
