@@ -48,8 +48,8 @@ BinView bin_view(void* base, int64_t R, int W, int H) {
     BinView b;
     char* p = reinterpret_cast<char*>(base);
     const size_t n = (size_t)(R > 0 ? R : 0);
+    b.values_sorted = carve<uint32_t>(p, n);  // first: the backward only needs this one, at offset 0 for any R
     b.keys_sorted = carve<uint64_t>(p, n);
-    b.values_sorted = carve<uint32_t>(p, n);
     b.keys_alt = carve<uint64_t>(p, n);
     b.values_alt = carve<uint32_t>(p, n);
     b.sort_scratch = carve<char>(p, sort_scratch_bytes(R));
@@ -160,36 +160,49 @@ int htgs_image_layout(int W, int H, size_t* offsets, int cap) {
     return k;
 }
 
-int htgs_forward_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
-                            const float* rotations, const float* opacities, const float* shs,
-                            const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
-                            const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
-                            int prefiltered, void* geom_buf, int* radii, int64_t* num_rendered_host, void* stream) {
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (num_rendered_host) *num_rendered_host = 0;
-    if (P < 0 || W <= 0 || H <= 0) { set_error("htgs_forward_preprocess: bad sizes P=%d W=%d H=%d", P, W, H); return 1; }
+static int forward_preprocess_impl(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
+                                   const float* rotations, const float* opacities, const float* shs,
+                                   const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                                   const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                                   int prefiltered, void* geom_buf, int* radii, cudaStream_t st, const char* who) {
+    if (P < 0 || W <= 0 || H <= 0) { set_error("%s: bad sizes P=%d W=%d H=%d", who, P, W, H); return 1; }
     if (P == 0) return 0;
-    if (!means3D || !opacities || !viewmatrix || !projmatrix || !campos || !geom_buf || !radii || !num_rendered_host) {
-        set_error("htgs_forward_preprocess: null required pointer");
+    if (!means3D || !opacities || !viewmatrix || !projmatrix || !campos || !geom_buf || !radii) {
+        set_error("%s: null required pointer", who);
         return 1;
     }
     if (!shs && !colors_precomp) {
-        // reference: "For non-RGB, provide precomputed Gaussian colors!" is the closest it gets; the plugin
-        // layer raises before reaching here (diff_gaussian_rasterization/__init__.py:194-195)
-        set_error("htgs_forward_preprocess: need shs or colors_precomp");
+        // the plugin layer raises before reaching here (diff_gaussian_rasterization/__init__.py:194-195)
+        set_error("%s: need shs or colors_precomp", who);
         return 1;
     }
-    if (!cov3D_precomp && (!scales || !rotations)) { set_error("htgs_forward_preprocess: need scales+rotations or cov3D_precomp"); return 1; }
-    if (D < 0 || D > 3) { set_error("htgs_forward_preprocess: sh degree %d outside 0..3", D); return 1; }
-    if (shs && !colors_precomp && M < (D + 1) * (D + 1)) { set_error("htgs_forward_preprocess: M=%d too small for degree %d", M, D); return 1; }
-    if (!aligned256(geom_buf)) { set_error("htgs_forward_preprocess: geom_buf must be 256-byte aligned"); return 1; }
-    if (rotations && (reinterpret_cast<size_t>(rotations) & 15)) { set_error("htgs_forward_preprocess: rotations must be 16-byte aligned"); return 1; }
+    if (!cov3D_precomp && (!scales || !rotations)) { set_error("%s: need scales+rotations or cov3D_precomp", who); return 1; }
+    if (D < 0 || D > 3) { set_error("%s: sh degree %d outside 0..3", who, D); return 1; }
+    if (shs && !colors_precomp && M < (D + 1) * (D + 1)) { set_error("%s: M=%d too small for degree %d", who, M, D); return 1; }
+    if (!aligned256(geom_buf)) { set_error("%s: geom_buf must be 256-byte aligned", who); return 1; }
+    if (rotations && (reinterpret_cast<size_t>(rotations) & 15)) { set_error("%s: rotations must be 16-byte aligned", who); return 1; }
     GeomView g = geom_view(geom_buf, P);
     { StageTimer t(ST_PREPROCESS, st);
     if (launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp, colors_precomp,
                           viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, g, radii, st)) return 1; }
     { StageTimer t(ST_SCAN, st);
     if (launch_scan_block_sums(P, g, st)) return 1; }
+    return 0;
+}
+
+int htgs_forward_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
+                            const float* rotations, const float* opacities, const float* shs,
+                            const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                            const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                            int prefiltered, void* geom_buf, int* radii, int64_t* num_rendered_host, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (!num_rendered_host) { set_error("htgs_forward_preprocess: null num_rendered_host"); return 1; }
+    *num_rendered_host = 0;
+    if (forward_preprocess_impl(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp,
+                                colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, geom_buf,
+                                radii, st, "htgs_forward_preprocess")) return 1;
+    if (P == 0) return 0;
+    GeomView g = geom_view(geom_buf, P);
     uint32_t r32 = 0;
     HTGS_CUDA_CHECK(cudaMemcpyAsync(&r32, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     HTGS_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -197,23 +210,43 @@ int htgs_forward_preprocess(int P, int D, int M, const float* means3D, const flo
     return 0;
 }
 
-int htgs_forward_render(int P, int64_t R, int W, int H, const float* background, const int* radii, void* geom_buf,
-                        void* binning_buf, void* image_buf, float* out_color, float* out_depth, float* out_alpha,
-                        void* stream) {
+int htgs_forward_preprocess_async(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
+                                  const float* rotations, const float* opacities, const float* shs,
+                                  const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                                  const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                                  int prefiltered, void* geom_buf, int* radii, uint32_t* num_rendered_pinned_host,
+                                  void* stream) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (!num_rendered_pinned_host) { set_error("htgs_forward_preprocess_async: null num_rendered_pinned_host"); return 1; }
+    if (forward_preprocess_impl(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp,
+                                colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, geom_buf,
+                                radii, st, "htgs_forward_preprocess_async")) return 1;
+    if (P == 0) { *num_rendered_pinned_host = 0; return 0; }
+    GeomView g = geom_view(geom_buf, P);
+    HTGS_CUDA_CHECK(cudaMemcpyAsync(num_rendered_pinned_host, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+// R_or_capacity sizes the binning buffer; with count_on_device the kernels read the true count from
+// the geometry buffer (written by the scan) and R_or_capacity is only an upper bound.
+static int forward_render_impl(int P, int64_t R_or_capacity, bool count_on_device, int W, int H, const float* background,
+                               const int* radii, void* geom_buf, void* binning_buf, void* image_buf, float* out_color,
+                               float* out_depth, float* out_alpha, cudaStream_t st, const char* who) {
+    const int64_t R = R_or_capacity;
     if (P <= 0) return 0;
     if (!background || !radii || !geom_buf || !image_buf || !out_color || !out_depth || !out_alpha || (R > 0 && !binning_buf)) {
-        set_error("htgs_forward_render: null required pointer");
+        set_error("%s: null required pointer", who);
         return 1;
     }
     if (!aligned256(geom_buf) || !aligned256(image_buf) || (R > 0 && !aligned256(binning_buf))) {
-        set_error("htgs_forward_render: work buffers must be 256-byte aligned");
+        set_error("%s: work buffers must be 256-byte aligned", who);
         return 1;
     }
-    if (R < 0 || R >= (int64_t(1) << 30)) { set_error("htgs_forward_render: R=%lld out of range", (long long)R); return 1; }
+    if (R < 0 || R >= (int64_t(1) << 30)) { set_error("%s: R=%lld out of range", who, (long long)R); return 1; }
     GeomView g = geom_view(geom_buf, P);
     ImgView img = img_view(image_buf, W, H);
     BinView b = bin_view(binning_buf, R, W, H);
+    const uint32_t* R_dev = count_on_device ? g.num_rendered : nullptr;
     const int gx = (W + HTGS_TILE - 1) / HTGS_TILE, gy = (H + HTGS_TILE - 1) / HTGS_TILE;
     if (R > 0) {
         const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));  // rasterizer_impl.cu:301-309
@@ -224,16 +257,31 @@ int htgs_forward_render(int P, int64_t R, int W, int H, const float* background,
         uint64_t* k1 = (passes & 1) ? b.keys_sorted : b.keys_alt;
         uint32_t* v1 = (passes & 1) ? b.values_sorted : b.values_alt;
         { StageTimer t(ST_MAKE_KEYS, st);
-        if (launch_make_keys(P, W, H, radii, g, k0, v0, st)) return 1; }
+        if (launch_make_keys(P, W, H, radii, g, k0, v0, R, st)) return 1; }
         { StageTimer t(ST_SORT, st);
-        if (sort_pairs(R, end_bit, k0, v0, k1, v1, b.sort_scratch, st)) return 1; }
+        if (sort_pairs(R, end_bit, k0, v0, k1, v1, b.sort_scratch, st, R_dev)) return 1; }
     }
     { StageTimer t(ST_TILE_RANGES, st);
-    if (launch_tile_ranges(R, W, H, b.keys_sorted, img.ranges, st)) return 1; }
+    if (launch_tile_ranges(R, R_dev, W, H, b.keys_sorted, img.ranges, st)) return 1; }
     { StageTimer t(ST_BLEND_FWD, st);
     if (launch_blend_forward(W, H, img.ranges, b.values_sorted, g, background, out_color, out_depth, out_alpha,
                              img.n_contrib, st)) return 1; }
     return 0;
+}
+
+int htgs_forward_render(int P, int64_t R, int W, int H, const float* background, const int* radii, void* geom_buf,
+                        void* binning_buf, void* image_buf, float* out_color, float* out_depth, float* out_alpha,
+                        void* stream) {
+    return forward_render_impl(P, R, false, W, H, background, radii, geom_buf, binning_buf, image_buf, out_color, out_depth,
+                               out_alpha, reinterpret_cast<cudaStream_t>(stream), "htgs_forward_render");
+}
+
+int htgs_forward_render_capacity(int P, int64_t capacity, int W, int H, const float* background, const int* radii,
+                                 void* geom_buf, void* binning_buf, void* image_buf, float* out_color, float* out_depth,
+                                 float* out_alpha, void* stream) {
+    if (capacity <= 0) { set_error("htgs_forward_render_capacity: capacity must be positive"); return 1; }
+    return forward_render_impl(P, capacity, true, W, H, background, radii, geom_buf, binning_buf, image_buf, out_color,
+                               out_depth, out_alpha, reinterpret_cast<cudaStream_t>(stream), "htgs_forward_render_capacity");
 }
 
 int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,

@@ -17,7 +17,7 @@ __global__ void __launch_bounds__(HTGS_PRE_BLOCK)
 make_keys_kernel(int P, int gx, int gy, const int* __restrict__ radii, const float2* __restrict__ means2D,
                  const float4* __restrict__ feat, const uint32_t* __restrict__ tiles_touched,
                  const uint32_t* __restrict__ block_offsets, uint32_t* __restrict__ point_offsets,
-                 uint64_t* __restrict__ keys, uint32_t* __restrict__ values) {
+                 uint64_t* __restrict__ keys, uint32_t* __restrict__ values, uint32_t capacity) {
     __shared__ uint32_t s_off[HTGS_PRE_BLOCK + 1];  // exclusive offsets inside the block
     __shared__ uint32_t s_warp[HTGS_PRE_BLOCK / 32];
     __shared__ uint32_t s_rect[HTGS_PRE_BLOCK];     // rmin.x | rmin.y<<12 | width<<24 .. packed below
@@ -69,17 +69,21 @@ make_keys_kernel(int P, int gx, int gy, const int* __restrict__ radii, const flo
         const uint32_t w = s_rectw[lo];
         const uint32_t row = k / w, col = k - row * w;
         const uint32_t tile = s_rect[lo] + row * (uint32_t)gx + col;
-        keys[(size_t)base + o] = ((uint64_t)tile << 32) | s_depth[lo];
-        values[(size_t)base + o] = (uint32_t)(blockIdx.x * HTGS_PRE_BLOCK + lo);
+        if (base + o < capacity) {  // only relevant when the buffers were sized from a predicted count
+            keys[(size_t)base + o] = ((uint64_t)tile << 32) | s_depth[lo];
+            values[(size_t)base + o] = (uint32_t)(blockIdx.x * HTGS_PRE_BLOCK + lo);
+        }
     }
 }
 
 // One thread per tile: lower bound of (tile << 32) in the sorted keys gives the
 // range start, lower bound of ((tile+1) << 32) its end.  Tiles with no
 // instances get (0,0) like the reference's memset.
-__global__ void tile_ranges_kernel(int64_t R, int tiles, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+__global__ void tile_ranges_kernel(int64_t R, const uint32_t* __restrict__ R_dev, int tiles,
+                                   const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= tiles) return;
+    if (R_dev) R = min(R, (int64_t)*R_dev);
     uint32_t bounds[2];
 #pragma unroll
     for (int s = 0; s < 2; s++) {
@@ -95,19 +99,20 @@ __global__ void tile_ranges_kernel(int64_t R, int tiles, const uint64_t* __restr
 }
 
 int launch_make_keys(int P, int W, int H, const int* radii, const GeomView& g, uint64_t* keys, uint32_t* values,
-                     cudaStream_t st) {
+                     int64_t capacity, cudaStream_t st) {
     const int gx = (W + HTGS_TILE - 1) / HTGS_TILE, gy = (H + HTGS_TILE - 1) / HTGS_TILE;
     const int nb = (P + HTGS_PRE_BLOCK - 1) / HTGS_PRE_BLOCK;
     make_keys_kernel<<<nb, HTGS_PRE_BLOCK, 0, st>>>(P, gx, gy, radii, g.means2D, g.feat, g.tiles_touched, g.block_sums,
-                                                    g.point_offsets, keys, values);
+                                                    g.point_offsets, keys, values, (uint32_t)capacity);
     HTGS_LAUNCH_CHECK("make_keys_kernel");
     return 0;
 }
 
-int launch_tile_ranges(int64_t R, int W, int H, const uint64_t* keys_sorted, uint2* ranges, cudaStream_t st) {
+int launch_tile_ranges(int64_t R, const uint32_t* R_dev, int W, int H, const uint64_t* keys_sorted, uint2* ranges,
+                       cudaStream_t st) {
     const int gx = (W + HTGS_TILE - 1) / HTGS_TILE, gy = (H + HTGS_TILE - 1) / HTGS_TILE;
     const int tiles = gx * gy;
-    tile_ranges_kernel<<<(tiles + 127) / 128, 128, 0, st>>>(R, tiles, keys_sorted, ranges);
+    tile_ranges_kernel<<<(tiles + 127) / 128, 128, 0, st>>>(R, R_dev, tiles, keys_sorted, ranges);
     HTGS_LAUNCH_CHECK("tile_ranges_kernel");
     return 0;
 }

@@ -70,8 +70,9 @@ int launch_preprocess(int P, int D, int M, const float* means3D, const float* sc
 int launch_scan_block_sums(int P, const GeomView& g, cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t st);
 int launch_make_keys(int P, int W, int H, const int* radii, const GeomView& g, uint64_t* keys, uint32_t* values,
-                     cudaStream_t st);
-int launch_tile_ranges(int64_t R, int W, int H, const uint64_t* keys_sorted, uint2* ranges, cudaStream_t st);
+                     int64_t capacity, cudaStream_t st);
+int launch_tile_ranges(int64_t R, const uint32_t* R_dev, int W, int H, const uint64_t* keys_sorted, uint2* ranges,
+                       cudaStream_t st);
 int launch_blend_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                          const float* bg, float* out_color, float* out_depth, float* out_alpha,
                          uint32_t* n_contrib, cudaStream_t st);
@@ -90,7 +91,7 @@ int launch_geom_backward(int P, int D, int M, const float* means3D, const int* r
 
 size_t sort_scratch_bytes(int64_t n);
 int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t* k_out, uint32_t* v_out,
-               void* scratch, cudaStream_t st);
+               void* scratch, cudaStream_t st, const uint32_t* n_dev = nullptr);
 // number of passes sort_pairs will run for end_bit (decides ping-pong parity)
 int sort_num_passes(int end_bit);
 

@@ -15,30 +15,20 @@ namespace htgs {
 
 __device__ __forceinline__ void store3(float* p, float a, float b, float c) { p[0] = a; p[1] = b; p[2] = c; }
 
-template <bool VEC>
-__device__ __forceinline__ void write_sh_grad(float* __restrict__ out, const float* w, int ncoef_active, int M,
+// Generic-layout fallback of the SH gradient store (any M): out[k*3 + c] = w[k] * g[c] for
+// k < ncoef_active, 0 above.  All indices into w[] are compile-time so it stays in registers.
+__device__ __forceinline__ void write_sh_grad(float* __restrict__ out, const float (&w)[16], int ncoef_active, int M,
                                               float g0, float g1, float g2) {
-    // out[k*3 + c] = w[k] * g[c] for k < ncoef_active, 0 above
-    const int total = M * 3;
-    if (VEC) {
-        float4* o4 = reinterpret_cast<float4*>(out);
-        for (int i = 0; i < total / 4; i++) {
-            float r[4];
 #pragma unroll
-            for (int t = 0; t < 4; t++) {
-                const int e = 4 * i + t, k = e / 3, c = e - 3 * k;
-                const float g = c == 0 ? g0 : (c == 1 ? g1 : g2);
-                r[t] = k < ncoef_active ? w[k] * g : 0.f;
-            }
-            o4[i] = make_float4(r[0], r[1], r[2], r[3]);
-        }
-    } else {
-        for (int e = 0; e < total; e++) {
-            const int k = e / 3, c = e - 3 * k;
-            const float g = c == 0 ? g0 : (c == 1 ? g1 : g2);
-            out[e] = k < ncoef_active ? w[k] * g : 0.f;
+    for (int k = 0; k < 16; k++) {
+        if (k < M) {
+            const float wk = k < ncoef_active ? w[k] : 0.f;
+            out[3 * k] = wk * g0;
+            out[3 * k + 1] = wk * g1;
+            out[3 * k + 2] = wk * g2;
         }
     }
+    for (int e = 48; e < 3 * M; e++) out[e] = 0.f;
 }
 
 __global__ void __launch_bounds__(256)
@@ -176,7 +166,33 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
         const float* sh = shs + (size_t)idx * M * 3;
         float w[16];
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;  // dL/ddir
-#define SHDOT(k) (sh[3 * (k)] * r0 + sh[3 * (k) + 1] * r1 + sh[3 * (k) + 2] * r2)
+        // s[k] = sh_k . dL/dRGB for the active coefficients.  Fast path (the HT layout, M == 16, 16-byte
+        // aligned): twelve 128-bit loads, dots formed on the fly so no 48-float copy lives in registers.
+        float sd[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) sd[k] = 0.f;
+        const int nact = (D + 1) * (D + 1);
+        const bool fast = (M == 16) && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0);
+        if (fast) {
+            const float4* sh4 = reinterpret_cast<const float4*>(sh);
+#pragma unroll
+            for (int i = 0; i < 12; i++) {
+                if (4 * i < 3 * nact) {
+                    const float4 v = __ldg(sh4 + i);
+                    const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int t = 0; t < 4; t++) {
+                        const int el = 4 * i + t, k = el / 3, c = el - 3 * k;
+                        sd[k] = fmaf(e[t], c == 0 ? r0 : (c == 1 ? r1 : r2), sd[k]);
+                    }
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; k++)
+                if (k < nact) sd[k] = sh[3 * k] * r0 + sh[3 * k + 1] * r1 + sh[3 * k + 2] * r2;
+        }
+#define SHDOT(k) (sd[k])
         w[0] = HTGS_SH_C0;
         int ncoef = 1;
         if (D > 0) {
@@ -220,8 +236,24 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
         }
 #undef SHDOT
         float* o = dL_dsh + (size_t)idx * M * 3;
-        if (sh_vec) write_sh_grad<true>(o, w, ncoef, M, r0, r1, r2);
-        else write_sh_grad<false>(o, w, ncoef, M, r0, r1, r2);
+        if (fast && sh_vec) {
+            // twelve 128-bit stores; coefficient and channel of every element are compile-time
+#pragma unroll
+            for (int k = 1; k < 16; k++)
+                if (k >= ncoef) w[k] = 0.f;
+            float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+            for (int i = 0; i < 12; i++) {
+                float e[4];
+#pragma unroll
+                for (int t = 0; t < 4; t++) {
+                    const int el = 4 * i + t, k = el / 3, c = el - 3 * k;
+                    e[t] = w[k] * (c == 0 ? r0 : (c == 1 ? r1 : r2));
+                }
+                o4[i] = make_float4(e[0], e[1], e[2], e[3]);
+            }
+        } else
+            write_sh_grad(o, w, ncoef, M, r0, r1, r2);
         // dnormvdv, auxiliary.h:107-117
         const float sum2 = ox * ox + oy * oy + oz * oz;
         const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);

@@ -56,8 +56,10 @@ static SortScratch carve(void* scratch, int64_t n) {
 }
 
 __global__ void __launch_bounds__(SORT_THREADS)
-sort_hist_kernel(const uint64_t* __restrict__ keys, int64_t n, int end_bit, int passes, uint32_t* __restrict__ hist) {
+sort_hist_kernel(const uint64_t* __restrict__ keys, int64_t n, const uint32_t* __restrict__ n_dev, int end_bit, int passes,
+                 uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_RADIX];
+    if (n_dev) n = min(n, (int64_t)*n_dev);  // device-side count (n is then the capacity)
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += SORT_THREADS) s_hist[i] = 0;
     __syncthreads();
     const int64_t stride = (int64_t)gridDim.x * SORT_THREADS;
@@ -103,11 +105,12 @@ __global__ void __launch_bounds__(SORT_RADIX) sort_scan_hist_kernel(uint32_t* __
     h[threadIdx.x] = e;
 }
 
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, 3)
 onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
-                uint32_t* __restrict__ vout, int64_t n, int shift, int nbits, const uint32_t* __restrict__ digit_start,
-                uint32_t* status, uint32_t* ticket, uint32_t* error) {
+                uint32_t* __restrict__ vout, int64_t n, const uint32_t* __restrict__ n_dev, int shift, int nbits,
+                const uint32_t* __restrict__ digit_start, uint32_t* status, uint32_t* ticket, uint32_t* error) {
     __shared__ uint64_t s_keys[SORT_TILE];
+    __shared__ uint8_t s_digit[SORT_TILE];
     __shared__ uint32_t s_whist[SORT_WARPS][SORT_RADIX];
     __shared__ uint32_t s_local_start[SORT_RADIX];
     __shared__ uint32_t s_goff[SORT_RADIX];
@@ -121,6 +124,8 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
     __syncthreads();
     const uint32_t tile = s_tile;
     const int64_t base = (int64_t)tile * SORT_TILE;
+    if (n_dev) n = min(n, (int64_t)*n_dev);  // grid was sized for the capacity; surplus tiles leave
+    if (base >= n) return;
     const int valid = (int)min((int64_t)SORT_TILE, n - base);
     const uint32_t mask = (1u << nbits) - 1u;
     const uint32_t lanemask_lt = (1u << lane) - 1u;
@@ -188,32 +193,29 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
     s_goff[tid] = digit_start[tid] + excl - local_start;
     __syncthreads();
 
-    // tile-local sorted order in shared memory; the value pass re-uses the key
-    // buffer (keeps the CTA under the 48 KB static limit -> more CTAs per SM)
+    // tile-local sorted order in shared memory.  Registers are the occupancy limit of this kernel, so
+    // nothing but the keys and their 16-bit positions is kept live: the digit of every sorted slot is
+    // parked in shared memory (1 B each) so the value pass can find its destination again, and the
+    // values are only loaded once the keys have left, re-using the key buffer.
 #pragma unroll
     for (int i = 0; i < SORT_IPT; i++) {
         const uint32_t d = (uint32_t)(k[i] >> shift) & mask;
         const uint32_t p = s_local_start[d] + s_whist[warp][d] + pos[i];
         pos[i] = (uint16_t)p;
         s_keys[p] = k[i];
+        s_digit[p] = (uint8_t)d;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < SORT_IPT; m++) {
+        const int j = tid + m * SORT_THREADS;
+        if (j < valid) kout[s_goff[s_digit[j]] + (uint32_t)j] = s_keys[j];
     }
     uint32_t v[SORT_IPT];
 #pragma unroll
     for (int i = 0; i < SORT_IPT; i++) {
         const int64_t idx = my0 + i * 32;
         v[i] = idx < n ? vin[idx] : 0u;
-    }
-    __syncthreads();
-    uint32_t dst[SORT_IPT];
-#pragma unroll
-    for (int m = 0; m < SORT_IPT; m++) {
-        const int j = tid + m * SORT_THREADS;
-        if (j < valid) {
-            const uint64_t key = s_keys[j];
-            const uint32_t d = (uint32_t)(key >> shift) & mask;
-            dst[m] = s_goff[d] + (uint32_t)j;
-            kout[dst[m]] = key;
-        }
     }
     __syncthreads();
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
@@ -223,7 +225,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
 #pragma unroll
     for (int m = 0; m < SORT_IPT; m++) {
         const int j = tid + m * SORT_THREADS;
-        if (j < valid) vout[dst[m]] = s_vals[j];
+        if (j < valid) vout[s_goff[s_digit[j]] + (uint32_t)j] = s_vals[j];
     }
 }
 
@@ -234,12 +236,14 @@ __global__ void sort_check_error_kernel(const uint32_t* error) {
     }
 }
 
-// Sorts on key bits [0, end_bit).  After the call the sorted pairs are in
+// Sorts on key bits [0, end_bit).  With n_dev != nullptr the element count is read on the device
+// (min(n, *n_dev)); n is then only the capacity the grid and the scratch were sized for, which lets
+// the caller enqueue the sort before the count has reached the host.  After the call the sorted pairs are in
 // (k_out, v_out) when the pass count is odd and in (k_in, v_in) when it is
 // even -- callers pick the starting buffer with sort_num_passes() so the result
 // lands where they want it.
 int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t* k_out, uint32_t* v_out,
-               void* scratch, cudaStream_t st) {
+               void* scratch, cudaStream_t st, const uint32_t* n_dev) {
     if (n <= 0) return 0;
     if (n >= (int64_t(1) << 30)) {
         set_error("sort_pairs: n=%lld exceeds the 2^30 limit of the look-back words", (long long)n);
@@ -255,14 +259,14 @@ int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t*
     const size_t zero_bytes = header_bytes() + (size_t)passes * tiles * SORT_RADIX * sizeof(uint32_t);
     HTGS_CUDA_CHECK(cudaMemsetAsync(scratch, 0, zero_bytes, st));
     const int hist_blocks = (int)std::min<int64_t>(tiles, 148 * 8);
-    sort_hist_kernel<<<hist_blocks, SORT_THREADS, 0, st>>>(k_in, n, end_bit, passes, s.hist);
+    sort_hist_kernel<<<hist_blocks, SORT_THREADS, 0, st>>>(k_in, n, n_dev, end_bit, passes, s.hist);
     HTGS_LAUNCH_CHECK("sort_hist_kernel");
     sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, st>>>(s.hist);
     HTGS_LAUNCH_CHECK("sort_scan_hist_kernel");
     uint64_t* ka = k_in; uint32_t* va = v_in; uint64_t* kb = k_out; uint32_t* vb = v_out;
     for (int p = 0; p < passes; p++) {
         const int nbits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
-        onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, st>>>(ka, va, kb, vb, n, 8 * p, nbits, s.hist + p * SORT_RADIX,
+        onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, st>>>(ka, va, kb, vb, n, n_dev, 8 * p, nbits, s.hist + p * SORT_RADIX,
                                                                    s.status + (size_t)p * tiles * SORT_RADIX,
                                                                    s.tickets + p, s.error);
         HTGS_LAUNCH_CHECK("onesweep_kernel");

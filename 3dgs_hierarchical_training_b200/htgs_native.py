@@ -25,6 +25,11 @@ _SIGNATURES = {
     "htgs_forward_preprocess": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,
                                         c_int, c_void_p, c_void_p, ctypes.POINTER(c_int64), c_void_p]),
+    "htgs_forward_preprocess_async": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+                                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,
+                                              c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_forward_render_capacity": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                             c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_forward_render": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_backward": (c_int, [c_int, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -117,6 +122,20 @@ def geom_layout(P):
 
 def binning_layout(R, W, H):
     return _layout(lib().htgs_binning_layout, BIN_FIELDS, R, W, H)
+
+
+def binning_capacity_from_bytes(nbytes, W, H):
+    """Largest instance count whose binning buffer has exactly this size (buffers sized from a
+    predicted count are laid out by that capacity, not by the true R)."""
+    l = lib()
+    lo, hi = 0, 1 << 30
+    while lo < hi:  # largest c with bytes(c) <= nbytes
+        mid = (lo + hi + 1) >> 1
+        if l.htgs_binning_bytes(mid, W, H) <= nbytes:
+            lo = mid
+        else:
+            hi = mid - 1
+    return lo
 
 
 def image_layout(W, H):

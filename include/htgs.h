@@ -62,7 +62,7 @@ enum {
 };
 enum {
     HTGS_BIN_KEYS_SORTED = 0,  /* uint64[R] */
-    HTGS_BIN_VALUES_SORTED,    /* uint32[R]  == point_list */
+    HTGS_BIN_VALUES_SORTED,    /* uint32[R]  == point_list; physically first (offset 0) */
     HTGS_BIN_KEYS_ALT,         /* uint64[R]  ping-pong partner */
     HTGS_BIN_VALUES_ALT,       /* uint32[R] */
     HTGS_BIN_SORT_SCRATCH,     /* histograms + look-back state */
@@ -98,6 +98,34 @@ int htgs_forward_preprocess(int P, int D, int M,
 int htgs_forward_render(int P, int64_t R, int W, int H, const float* background,
                         const int* radii, void* geom_buf, void* binning_buf, void* image_buf,
                         float* out_color, float* out_depth, float* out_alpha, void* stream);
+
+/* ---- forward without the host round trip ----
+ * The reference stalls the host on a 4-byte copy of R in every forward (rasterizer_impl.cu:282)
+ * because R sizes the binning buffer.  These two entry points let the caller size that buffer
+ * from a PREDICTION (e.g. the previous frame's R plus a margin) and enqueue the whole forward
+ * without waiting:
+ *   htgs_forward_preprocess_async   same as htgs_forward_preprocess but no synchronisation; R is
+ *                                   copied asynchronously into *num_rendered_pinned_host (must be
+ *                                   pinned host memory; valid once the stream reached this point,
+ *                                   e.g. after an event recorded right after the call);
+ *   htgs_forward_render_capacity    same as htgs_forward_render with a binning buffer sized by
+ *                                   htgs_binning_bytes(capacity, W, H); the kernels take the true R
+ *                                   from device memory.  If R turns out larger than capacity nothing
+ *                                   is written out of bounds but the outputs are invalid: the caller
+ *                                   checks R <= capacity afterwards and, if not, reruns
+ *                                   htgs_forward_render with an exact-size buffer.
+ * The backward reads only the sorted Gaussian list, which sits at offset 0 of the binning buffer
+ * for every capacity, so htgs_backward needs no knowledge of the capacity that was used. */
+int htgs_forward_preprocess_async(int P, int D, int M,
+                                  const float* means3D, const float* scales, float scale_modifier,
+                                  const float* rotations, const float* opacities, const float* shs,
+                                  const float* cov3D_precomp, const float* colors_precomp,
+                                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                                  int W, int H, float tanfovx, float tanfovy, int prefiltered,
+                                  void* geom_buf, int* radii, uint32_t* num_rendered_pinned_host, void* stream);
+int htgs_forward_render_capacity(int P, int64_t capacity, int W, int H, const float* background,
+                                 const int* radii, void* geom_buf, void* binning_buf, void* image_buf,
+                                 float* out_color, float* out_depth, float* out_alpha, void* stream);
 
 /* ---- backward ----
  * Replaces Rasterizer::backward (rasterizer_impl.cu:343-447; backward.cu).

@@ -32,7 +32,8 @@ def bits_equal(a, b):
 
 def view_state(geom, binning, img, P, R, W, H):
     """Typed views of the opaque work buffers through the layout queries of the C ABI."""
-    gl, bl, il = nat.geom_layout(P), nat.binning_layout(R, W, H), nat.image_layout(W, H)
+    cap = nat.binning_capacity_from_bytes(binning.numel(), W, H) if R > 0 else 0
+    gl, bl, il = nat.geom_layout(P), nat.binning_layout(cap, W, H), nat.image_layout(W, H)
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
 
     def sl(buf, off, n, dtype):
