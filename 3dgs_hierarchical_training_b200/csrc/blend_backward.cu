@@ -175,15 +175,20 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 for (int k = 0; k < BWD_NV; k++) v[k] = 0.f;
                 if (live) {
                     const float2 q2 = lds64(a + 32);  // b, depth
+                    // T = T / (1 - alpha), backward.cu:534.  One Newton step on the hardware reciprocal
+                    // (<= 1 ulp from div.rn, 4 issue slots instead of 10); also feeds the background term.
                     const float one_m_a = SB(1.f, alpha);
-                    T = __fdiv_rn(T, one_m_a);                                   // backward.cu:534
+                    float rinv;
+                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(one_m_a));
+                    rinv = fmaf(fmaf(-one_m_a, rinv, 1.f), rinv, rinv);
+                    T = T * rinv;
                     const float aT = alpha * T;
                     const float Cd = fmaf(q2.y, dd, fmaf(q2.x, d2, fmaf(q1.w, d1, fmaf(q1.z, d0, da))));
                     A = fmaf(last_alpha, Cprev, (1.f - last_alpha) * A);
                     Cprev = Cd;
                     last_alpha = alpha;
                     float dL_dopa = (Cd - A) * T;
-                    if (warp_has_bg) dL_dopa += __fdividef(bg_k, one_m_a);
+                    if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
                     const float w = G * dL_dopa;
                     const float wdx = w * dx, wdy = w * dy;
                     v[0] = w;          // -> dL/dopacity, and scaled by opacity the common factor below
