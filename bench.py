@@ -105,6 +105,28 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", {}
 
 
+def ncu_traffic_bytes(kernel_stage, workload):
+    """DRAM read+write bytes per launch of the stage's kernel from the committed ncu --set full summary
+    (profiles/r01_ncu_full_config3_summary.csv); None when no capture exists for this workload."""
+    name = {"blend_bwd": "blend_backward_kernel", "blend_fwd": "blend_forward_kernel", "preprocess": "preprocess_kernel",
+            "geom_bwd": "geom_backward_kernel", "sort": "onesweep_kernel#1"}.get(kernel_stage)
+    path = os.path.join(ROOT, "profiles", f"r01_ncu_full_{workload}_summary.csv")
+    if not name or not os.path.exists(path):
+        return None
+    try:
+        lines = [l for l in open(path).read().splitlines() if l and not l.startswith("#")]
+        hdr = lines[0].split(",")
+        ri = next(i for i, c in enumerate(hdr) if c.startswith("dram__bytes_read.sum"))
+        wi = next(i for i, c in enumerate(hdr) if c.startswith("dram__bytes_write.sum"))
+        for l in lines[1:]:
+            c = l.split(",")
+            if name in c[0]:
+                return int((float(c[ri]) + float(c[wi])) * 1e6)
+    except Exception:
+        return None
+    return None
+
+
 def stage_bytes(P, P_vis, R, tiles, M, passes):
     """Algorithmic HBM bytes per launch of the streaming stages."""
     sh = 12 * M
@@ -264,13 +286,13 @@ def run_ours(args, rank, world, local_rank):
         flops = (22 * n_ref_tested + 11 * n_blended) if dom == "blend_fwd" else (22 * n_ref_tested + 70 * n_blended)
         ach = flops / (per[dom] * 1e-3) / 1e12
         roofline = {"kernel": dom, "bound": "fp32", "achieved": round(ach, 3), "peak": round(fp32_peak_tflops, 2),
-                    "unit": "TFLOP/s", "frac": round(ach / fp32_peak_tflops, 4), "traffic": None,
+                    "unit": "TFLOP/s", "frac": round(ach / fp32_peak_tflops, 4), "traffic": ncu_traffic_bytes(dom, args.workload),
                     "peak_source": f"148 SMs x 128 lanes x 2 x {sm_mhz} MHz (clock sampled during the run); no tensor cores on this path",
                     "work": "reference-algorithm FLOPs of the pairs the reference loop tests/blends"}
     else:
         ach = by[dom] / (per[dom] * 1e-3) / 1e9
         roofline = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak, "unit": "GB/s",
-                    "frac": round(ach / hbm_peak, 4), "traffic": None, "peak_source": peak_src}
+                    "frac": round(ach / hbm_peak, 4), "traffic": ncu_traffic_bytes(dom, args.workload), "peak_source": peak_src}
     out = {
         "metric": "fwd+bwd rasterize views/s (1M Gaussians SH3 1080p per view)" if args.workload == "config3" else f"fwd+bwd rasterize views/s ({args.workload})",
         "value": world * 1e3 / ms_per_step, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
