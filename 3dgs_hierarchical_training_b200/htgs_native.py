@@ -12,6 +12,12 @@ LIB_PATH = os.path.join(_HERE, "libhtgs.so")
 
 c_void_p, c_int, c_int64, c_float, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
 
+class AdamGroup(ctypes.Structure):
+    """htgs_adam_group of include/htgs.h."""
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("numel", ctypes.c_longlong), ("lr", c_float)]
+
+
 _SIGNATURES = {
     "htgs_abi_version": (c_int, []),
     "htgs_last_error": (ctypes.c_char_p, []),
@@ -43,6 +49,8 @@ _SIGNATURES = {
     "htgs_profile_enable": (None, [c_int]),
     "htgs_profile_read": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int), c_int]),
     "htgs_blend_stats": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_densification_stats": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_adam_step": (c_int, [c_int, ctypes.POINTER(AdamGroup), c_float, c_float, c_float, ctypes.c_longlong, c_void_p]),
     "htgs_dist2_workspace_bytes": (c_size_t, [c_int]),
     "htgs_dist2": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
 }

@@ -196,6 +196,28 @@ int htgs_profile_read(double* ms_sum, int* counts, int cap);
 int htgs_blend_stats(int P, int64_t R, int W, int H, const void* geom_buf, const void* binning_buf,
                      const void* image_buf, unsigned long long* stats3, void* stream);
 
+/* ---- per-step tail after the backward (opt-in, outside the plugin surface) ----
+ * htgs_densification_stats replaces the three boolean-mask updates of
+ * trainer/ht3dgs_trainer.py:143-148 + scene/gaussian_model_ht.py:718-721 (each of which syncs the host):
+ * for radii[i] > 0:  max_radii2D[i] = max(max_radii2D[i], radii[i]);
+ *                    xyz_gradient_accum[i] += ||grad_means2D[i, 0:2]||;  denom[i] += 1.
+ * htgs_adam_step is one fused launch for all parameter groups of the torch.optim.Adam the model builds at
+ * scene/gaussian_model_ht.py:275-289 (betas, eps shared; lr per group; no weight decay / amsgrad), `step`
+ * counting from 1.  Group structs are read on the host; pointers inside are device pointers. */
+#define HTGS_ADAM_MAX_GROUPS 8
+typedef struct htgs_adam_group {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    long long numel;
+    float lr;
+} htgs_adam_group;
+int htgs_densification_stats(int P, const int* radii, const float* grad_means2D, float* max_radii2D,
+                             float* xyz_gradient_accum, float* denom, void* stream);
+int htgs_adam_step(int n_groups, const htgs_adam_group* groups, float beta1, float beta2, float eps,
+                   long long step, void* stream);
+
 /* ---- simple-knn ----
  * Replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:15-26,
  * simple_knn.cu:186-222): out[i] = mean of the squared distances from point i
