@@ -51,6 +51,9 @@ _SIGNATURES = {
     "htgs_blend_stats": (c_int, [c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_densification_stats": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_adam_step": (c_int, [c_int, ctypes.POINTER(AdamGroup), c_float, c_float, c_float, ctypes.c_longlong, c_void_p]),
+    "htgs_l1_ssim_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "htgs_l1_ssim_forward": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_l1_ssim_backward": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p]),
     "htgs_dist2_workspace_bytes": (c_size_t, [c_int]),
     "htgs_dist2": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
 }

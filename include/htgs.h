@@ -218,6 +218,18 @@ int htgs_densification_stats(int P, const int* radii, const float* grad_means2D,
 int htgs_adam_step(int n_groups, const htgs_adam_group* groups, float beta1, float beta2, float eps,
                    long long step, void* stream);
 
+/* ---- image loss (opt-in) ----
+ * loss = (1 - lambda) * mean|pred - gt| + lambda * (1 - SSIM(pred, gt)), the training loss of
+ * trainer/losses.py:98-136 (SSIM: 11x11 sigma-1.5 window, zero padding, per channel, :147-200), for
+ * pred/gt float32 [C,H,W].  forward writes out3 = {loss, l1, 1-ssim} (device) and, when dmaps != NULL,
+ * the three derivative maps [3][C][H][W] the backward consumes; backward writes dL_dpred[C,H,W] =
+ * grad_loss * dloss/dpred (grad_loss: device scalar, NULL = 1).  scratch from htgs_l1_ssim_scratch_bytes. */
+size_t htgs_l1_ssim_scratch_bytes(int C, int H, int W);
+int htgs_l1_ssim_forward(int C, int H, int W, const float* pred, const float* gt, float lambda_dssim,
+                         float* dmaps, void* scratch, float* out3, void* stream);
+int htgs_l1_ssim_backward(int C, int H, int W, const float* pred, const float* gt, const float* dmaps,
+                          float lambda_dssim, const float* grad_loss, float* dL_dpred, void* stream);
+
 /* ---- simple-knn ----
  * Replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:15-26,
  * simple_knn.cu:186-222): out[i] = mean of the squared distances from point i
