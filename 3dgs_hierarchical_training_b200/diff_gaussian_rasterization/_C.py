@@ -23,6 +23,32 @@ SPECULATIVE = True
 CAPACITY_MARGIN = 1.25
 
 
+# Optional gradient arena (view-parallel training): when set, the backward writes the five parameter
+# gradients straight into slices of one flat buffer (the one that is all-reduced) instead of fresh tensors,
+# which removes the 236 B/Gaussian pack copy before the collective.  Only meaningful when every parameter
+# receives one backward per step; see htgs_dist.FlatGradReducer.
+_GRAD_ARENA = None
+
+
+def set_grad_arena(flat, slices):
+    """flat: 1-D float32 CUDA tensor; slices: {"means3D"|"shs"|"opacities"|"scales"|"rotations": (lo, hi)}.
+    Pass (None, None) to clear."""
+    global _GRAD_ARENA
+    _GRAD_ARENA = None if flat is None else (flat, dict(slices))
+
+
+def _arena_or_empty(name, shape, **opts):
+    if _GRAD_ARENA is not None:
+        flat, slices = _GRAD_ARENA
+        rng = slices.get(name)
+        n = 1
+        for v in shape:
+            n *= v
+        if rng is not None and rng[1] - rng[0] == n and flat.device == opts["device"]:
+            return flat[rng[0]:rng[1]].view(shape)  # a fresh view object: autograd may adopt it as .grad
+    return torch.empty(shape, **opts)
+
+
 def _pinned_counter(dev):
     t = _PINNED_R.get(dev.index)
     if t is None:
@@ -144,15 +170,15 @@ def backward_impl(background, means3D, radii, colors, scales, rotations, scale_m
     with torch.cuda.device(dev):
         st = _stream(dev)
         dmeans2D = torch.empty((P, 3), **f32)
-        dopacity = torch.empty((P, 1), **f32)
-        dmeans3D = torch.empty((P, 3), **f32)
+        dopacity = _arena_or_empty("opacities", (P, 1), **f32)
+        dmeans3D = _arena_or_empty("means3D", (P, 3), **f32)
         want_colors = has_colors or mirror_all
         want_cov = has_cov or mirror_all
         dcolors = torch.empty((P, NUM_CHANNELS), **f32) if want_colors else None
         dcov3D = torch.empty((P, 6), **f32) if want_cov else None
-        dsh = torch.empty((P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
-        dscales = torch.empty((P, 3), **f32) if has_scales else torch.zeros((P, 3), **f32)
-        drot = torch.empty((P, 4), **f32) if has_scales else torch.zeros((P, 4), **f32)
+        dsh = _arena_or_empty("shs", (P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
+        dscales = _arena_or_empty("scales", (P, 3), **f32) if has_scales else torch.zeros((P, 3), **f32)
+        drot = _arena_or_empty("rotations", (P, 4), **f32) if has_scales else torch.zeros((P, 4), **f32)
         scratch = torch.empty(lib.htgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
         nat.check(lib.htgs_backward(
             P, int(degree), M, int(R), W, H, nat.ptr(background), nat.ptr(means3D), nat.ptr(sh), nat.ptr(colors),

@@ -35,6 +35,31 @@ class FlatGradReducer:
             o += P * per
         assert o == self.flat.numel()
 
+    def install_arena(self):
+        """Let the rasterizer backward write its gradients directly into this buffer (no pack copy).
+        Valid when each parameter gets exactly one backward per step."""
+        from diff_gaussian_rasterization import _C
+        _C.set_grad_arena(self.flat, self.slices)
+
+    @staticmethod
+    def remove_arena():
+        from diff_gaussian_rasterization import _C
+        _C.set_grad_arena(None, None)
+
+    def pack_if_needed(self, grads):
+        """Copies only the gradients that autograd did not adopt in place from the arena; returns how many were copied."""
+        copied = 0
+        for name in PARAM_ORDER:
+            lo, hi = self.slices[name]
+            g = grads[name]
+            if g is None:
+                self.flat[lo:hi].zero_()
+                copied += 1
+            elif g.data_ptr() != self.flat.data_ptr() + 4 * lo:
+                self.flat[lo:hi].copy_(g.reshape(-1))
+                copied += 1
+        return copied
+
     def pack(self, grads):
         for name in PARAM_ORDER:
             lo, hi = self.slices[name]

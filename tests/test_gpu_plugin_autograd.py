@@ -94,3 +94,34 @@ def test_forward_only_no_grad_and_colors_precomp_grad_slot():
     color.sum().backward()
     assert colors.grad is not None and colors.grad.shape == colors.shape and bool((colors.grad >= 0).all())
     assert not colors.grad[radii == 0].any()
+
+
+def test_gradient_arena_is_adopted_and_equal():
+    """htgs_dist.FlatGradReducer.install_arena: the backward writes into the flat all-reduce buffer and autograd
+    adopts those views as .grad (no pack copy); values equal the ordinary path."""
+    import htgs_dist
+    cfg, scene, cam, up, bg, rast = _setup("small")
+    dev = torch.device("cuda:0")
+    P = cfg["P"]
+
+    def run():
+        p = {k: scene[k].clone().requires_grad_(True) for k in htgs_dist.PARAM_ORDER}
+        out = rast(means3D=p["means3D"], means2D=torch.zeros_like(p["means3D"], requires_grad=True), opacities=p["opacities"],
+                   shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+        torch.autograd.backward((out[0], out[2], out[3]), (up["dL_dcolor"], up["dL_ddepth"], up["dL_dalpha"]))
+        return p
+
+    plain = run()
+    red = htgs_dist.FlatGradReducer(P, dev)
+    red.install_arena()
+    try:
+        arena = run()
+        copied = red.pack_if_needed({k: arena[k].grad for k in htgs_dist.PARAM_ORDER})
+    finally:
+        red.remove_arena()
+    assert copied == 0, "autograd did not adopt the arena views"
+    views = red.unpack({k: plain[k] for k in htgs_dist.PARAM_ORDER})
+    for k in htgs_dist.PARAM_ORDER:
+        assert rel_inf(views[k], plain[k].grad) <= GRAD_RTOL, k
+    again = run()  # arena removed: ordinary allocation again
+    assert again["shs"].grad.data_ptr() != red.flat.data_ptr() + 4 * red.slices["shs"][0]
