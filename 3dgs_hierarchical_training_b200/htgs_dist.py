@@ -79,3 +79,36 @@ class FlatGradReducer:
 
     def unpack(self, like):
         return {name: self.flat[lo:hi].view_as(like[name]) for name, (lo, hi) in self.slices.items()}
+
+
+def reduce_densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom):
+    """Densification statistics for one data-parallel step ("things that must also be
+    reduced"): every rank contributes the view it rendered, every replica ends with the same state a single
+    process would hold after visiting all those views one after another
+    (ht3dgs_trainer.py:143-148 + gaussian_model_ht.py:718-721 per view):
+
+        xyz_gradient_accum += sum over ranks of ||viewspace_grad[:, :2]|| where radii > 0      (SUM)
+        denom              += number of ranks that saw the Gaussian                            (SUM)
+        max_radii2D         = max(max_radii2D, max over ranks of radii where radii > 0)        (MAX)
+
+    Per-rank increments are built first (on CUDA by the fused statistics kernel into zeroed scratch), then one
+    SUM all-reduce of 8 B/Gaussian and one MAX all-reduce of 4 B/Gaussian, then applied in place.  Without an
+    initialised process group (or world size 1) it degenerates to the single-view update."""
+    P = int(radii.numel())
+    dev = radii.device
+    inc = torch.zeros(2, P, device=dev, dtype=torch.float32)  # [0] gradient-norm increment, [1] visit count
+    rad = torch.zeros(P, device=dev, dtype=torch.float32)
+    if radii.is_cuda:
+        from htgs_optim import add_densification_stats
+        add_densification_stats(radii.contiguous(), viewspace_grad.contiguous(), rad, inc[0], inc[1])
+    else:  # host tensors: the gloo tests of this logic
+        vis = radii > 0
+        inc[0] = torch.where(vis, torch.linalg.vector_norm(viewspace_grad[:, :2], dim=-1), inc[0])
+        inc[1] = vis.to(torch.float32)
+        rad = torch.where(vis, radii.to(torch.float32), rad)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(inc, op=dist.ReduceOp.SUM)
+        dist.all_reduce(rad, op=dist.ReduceOp.MAX)
+    xyz_gradient_accum.add_(inc[0].view_as(xyz_gradient_accum))
+    denom.add_(inc[1].view_as(denom))
+    torch.maximum(max_radii2D, rad.view_as(max_radii2D), out=max_radii2D)

@@ -180,7 +180,7 @@ def run_ours(args, rank, world, local_rank):
                                                  projmatrix=cam["projmatrix"], sh_degree=3, campos=cam["campos"],
                                                  prefiltered=False, debug=False)
 
-    def step(cam, upg):
+    def step(cam, upg, before_backward=None):
         for p in params.values():
             p.grad = None
         for cam_v in ([cam] if len(cams_d) == 1 else cams_d):
@@ -188,6 +188,8 @@ def run_ours(args, rank, world, local_rank):
             rast = dgr.GaussianRasterizer(settings(cam_v))
             color, radii, depth, alpha = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
                                               shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+            if before_backward is not None:
+                before_backward()
             torch.autograd.backward((color, depth, alpha), (upg["dL_dcolor"], upg["dL_ddepth"], upg["dL_dalpha"]))
         if world > 1:
             reducer.pack_if_needed({k: params[k].grad for k in htgs_dist.PARAM_ORDER})
@@ -238,12 +240,24 @@ def run_ours(args, rank, world, local_rank):
         h2d = sum(v.numel() * 4 for v in host.values()) + sum(v.numel() * 4 for v in host_cam.values())
         result = torch.zeros(1, dtype=torch.float64).pin_memory()
 
+        # The camera (140 B) is needed by the first kernel and goes on the compute stream.  The upstream
+        # image gradients (41 MB at 1080p) are only read by the backward, so their host->device copy runs
+        # on a second stream underneath the forward pass; the compute stream waits for it just before the
+        # backward.  The buffers stay referenced until the blocking result read below, so the allocator
+        # cannot hand them out again while either stream still uses them.
+        copy_stream = torch.cuda.Stream(device=dev)
+        copied = torch.cuda.Event()
+
         def e2e_step():
-            upg = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+            main = torch.cuda.current_stream(dev)
+            copy_stream.wait_stream(main)
+            with torch.cuda.stream(copy_stream):
+                upg = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+                copied.record(copy_stream)
             cam = dict(cam_h)
             for k, v in host_cam.items():
                 cam[k] = v.to(dev, non_blocking=True)
-            color, radii = step(cam, upg)
+            color, radii = step(cam, upg, before_backward=lambda: main.wait_event(copied))
             s = (color.detach().double().sum() + params["opacities"].grad.double().sum()).reshape(1)
             result.copy_(s, non_blocking=False)  # device->host read of the step's scalar result
             return float(result[0].detach())

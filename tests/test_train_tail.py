@@ -138,3 +138,21 @@ def test_densification_stats_matches_oracle():
     assert np.array_equal(d[4].squeeze(1).cpu().numpy(), o[2])
     with pytest.raises(RuntimeError):
         htgs_optim.add_densification_stats(radii, grad, max_r, acc, den)  # CPU tensors: no fallback
+
+
+@pytest.mark.gpu
+def test_reduce_densification_stats_single_rank_equals_direct_update():
+    """Without a process group the data-parallel wrapper must reduce to the plain per-view update."""
+    import htgs_dist
+    import htgs_optim
+    g = torch.Generator().manual_seed(12)
+    P = 20_011
+    radii = torch.randint(-3, 40, (P,), generator=g, dtype=torch.int32).clamp_min(0).cuda()
+    grad = torch.randn(P, 3, generator=g).cuda()
+    state = [torch.rand(P, generator=g) * 30, torch.rand(P, 1, generator=g), torch.rand(P, 1, generator=g).round()]
+    a = [t.clone().cuda() for t in state]
+    b = [t.clone().cuda() for t in state]
+    htgs_optim.add_densification_stats(radii, grad, *a)
+    htgs_dist.reduce_densification_stats(radii, grad, *b)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2])
+    assert torch.allclose(a[1], b[1], rtol=1e-6, atol=0)
