@@ -161,7 +161,7 @@ int htgs_image_layout(int W, int H, size_t* offsets, int cap) {
 }
 
 static int forward_preprocess_impl(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
-                                   const float* rotations, const float* opacities, const float* shs,
+                                   const float* rotations, const float* opacities, const float* shs, const float* shs_rest,
                                    const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
                                    const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
                                    int prefiltered, void* geom_buf, int* radii, cudaStream_t st, const char* who) {
@@ -183,7 +183,7 @@ static int forward_preprocess_impl(int P, int D, int M, const float* means3D, co
     if (rotations && (reinterpret_cast<size_t>(rotations) & 15)) { set_error("%s: rotations must be 16-byte aligned", who); return 1; }
     GeomView g = geom_view(geom_buf, P);
     { StageTimer t(ST_PREPROCESS, st);
-    if (launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+    if (launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, shs_rest, cov3D_precomp, colors_precomp,
                           viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, g, radii, st)) return 1; }
     { StageTimer t(ST_SCAN, st);
     if (launch_scan_block_sums(P, g, st)) return 1; }
@@ -198,7 +198,7 @@ int htgs_forward_preprocess(int P, int D, int M, const float* means3D, const flo
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (!num_rendered_host) { set_error("htgs_forward_preprocess: null num_rendered_host"); return 1; }
     *num_rendered_host = 0;
-    if (forward_preprocess_impl(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp,
+    if (forward_preprocess_impl(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, nullptr, cov3D_precomp,
                                 colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, geom_buf,
                                 radii, st, "htgs_forward_preprocess")) return 1;
     if (P == 0) return 0;
@@ -218,9 +218,31 @@ int htgs_forward_preprocess_async(int P, int D, int M, const float* means3D, con
                                   void* stream) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (!num_rendered_pinned_host) { set_error("htgs_forward_preprocess_async: null num_rendered_pinned_host"); return 1; }
-    if (forward_preprocess_impl(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp,
+    if (forward_preprocess_impl(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, nullptr, cov3D_precomp,
                                 colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, prefiltered, geom_buf,
                                 radii, st, "htgs_forward_preprocess_async")) return 1;
+    if (P == 0) { *num_rendered_pinned_host = 0; return 0; }
+    GeomView g = geom_view(geom_buf, P);
+    HTGS_CUDA_CHECK(cudaMemcpyAsync(num_rendered_pinned_host, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+int htgs_forward_preprocess_raw_async(int P, int D, const float* xyz, const float* scaling_raw, float scale_modifier,
+                                      const float* rotation_raw, const float* opacity_raw, const float* features_dc,
+                                      const float* features_rest, const float* viewmatrix, const float* projmatrix,
+                                      const float* campos, int W, int H, float tanfovx, float tanfovy, int prefiltered,
+                                      void* geom_buf, int* radii, uint32_t* num_rendered_pinned_host, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const char* who = "htgs_forward_preprocess_raw_async";
+    if (!num_rendered_pinned_host) { set_error("%s: null num_rendered_pinned_host", who); return 1; }
+    if (P > 0 && (!scaling_raw || !rotation_raw || !opacity_raw || !features_dc || !features_rest)) {
+        set_error("%s: null parameter pointer", who);
+        return 1;
+    }
+    if (reinterpret_cast<size_t>(features_rest) & 15) { set_error("%s: features_rest must be 16-byte aligned", who); return 1; }
+    if (forward_preprocess_impl(P, D, 16, xyz, scaling_raw, scale_modifier, rotation_raw, opacity_raw, features_dc,
+                                features_rest, nullptr, nullptr, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy,
+                                prefiltered, geom_buf, radii, st, who)) return 1;
     if (P == 0) { *num_rendered_pinned_host = 0; return 0; }
     GeomView g = geom_view(geom_buf, P);
     HTGS_CUDA_CHECK(cudaMemcpyAsync(num_rendered_pinned_host, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -284,7 +306,8 @@ int htgs_forward_render_capacity(int P, int64_t capacity, int W, int H, const fl
                                out_depth, out_alpha, reinterpret_cast<cudaStream_t>(stream), "htgs_forward_render_capacity");
 }
 
-int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
+static int backward_impl(const char* who, const float* shs_rest, const float* opacity_raw, float* dL_dsh_rest,
+                         int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
                   const float* shs, const float* colors_precomp, const float* alphas, const float* scales,
                   float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
                   const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int* radii,
@@ -297,17 +320,17 @@ int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* bac
     if (!background || !means3D || !alphas || !viewmatrix || !projmatrix || !campos || !radii || !geom_buf || !image_buf ||
         !dL_dout_color || !dL_dout_depth || !dL_dout_alpha || !scratch || !dL_dmeans2D || !dL_dopacity || !dL_dmeans3D ||
         (R > 0 && !binning_buf)) {
-        set_error("htgs_backward: null required pointer");
+        set_error("%s: null required pointer", who);
         return 1;
     }
-    if (shs && !dL_dsh) { set_error("htgs_backward: dL_dsh required with shs"); return 1; }
-    if (colors_precomp && !dL_dcolors) { set_error("htgs_backward: dL_dcolors required with colors_precomp"); return 1; }
-    if (scales && (!rotations || !dL_dscales || !dL_drotations)) { set_error("htgs_backward: scale/rotation outputs required"); return 1; }
-    if (!scales && !cov3D_precomp) { set_error("htgs_backward: need scales+rotations or cov3D_precomp"); return 1; }
-    if (cov3D_precomp && !dL_dcov3D) { set_error("htgs_backward: dL_dcov3D required with cov3D_precomp"); return 1; }
-    if (!aligned256(scratch) || !aligned256(geom_buf) || !aligned256(image_buf)) { set_error("htgs_backward: buffers must be 256-byte aligned"); return 1; }
+    if (shs && !dL_dsh) { set_error("%s: dL_dsh required with shs", who); return 1; }
+    if (colors_precomp && !dL_dcolors) { set_error("%s: dL_dcolors required with colors_precomp", who); return 1; }
+    if (scales && (!rotations || !dL_dscales || !dL_drotations)) { set_error("%s: scale/rotation outputs required", who); return 1; }
+    if (!scales && !cov3D_precomp) { set_error("%s: need scales+rotations or cov3D_precomp", who); return 1; }
+    if (cov3D_precomp && !dL_dcov3D) { set_error("%s: dL_dcov3D required with cov3D_precomp", who); return 1; }
+    if (!aligned256(scratch) || !aligned256(geom_buf) || !aligned256(image_buf)) { set_error("%s: buffers must be 256-byte aligned", who); return 1; }
     if ((dL_drotations && (reinterpret_cast<size_t>(dL_drotations) & 15)) || (rotations && (reinterpret_cast<size_t>(rotations) & 15))) {
-        set_error("htgs_backward: rotations / dL_drotations must be 16-byte aligned");
+        set_error("%s: rotations / dL_drotations must be 16-byte aligned", who);
         return 1;
     }
     GeomView g = geom_view(const_cast<void*>(geom_buf), P);
@@ -323,10 +346,50 @@ int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* bac
     }
     // the SH path feeds dL/dcolour into dL/dsh; only the precomputed-colour path returns it
     StageTimer t(ST_GEOM_BWD, st);
-    if (launch_geom_backward(P, D, M, means3D, radii, shs, colors_precomp, scales, scale_modifier, rotations, cov3D_precomp,
+    if (launch_geom_backward(P, D, M, means3D, radii, shs, shs_rest, opacity_raw, dL_dsh_rest, colors_precomp, scales, scale_modifier, rotations, cov3D_precomp,
                              viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, g, gacc, dL_dmeans2D, dL_dopacity,
                              dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, st)) return 1;
     return 0;
+}
+
+int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
+                  const float* shs, const float* colors_precomp, const float* alphas, const float* scales,
+                  float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                  const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int* radii,
+                  const void* geom_buf, const void* binning_buf, const void* image_buf, const float* dL_dout_color,
+                  const float* dL_dout_depth, const float* dL_dout_alpha, void* scratch, float* dL_dmeans2D,
+                  float* dL_dopacity, float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                  float* dL_dscales, float* dL_drotations, void* stream) {
+    return backward_impl("htgs_backward", nullptr, nullptr, nullptr, P, D, M, R, W, H, background, means3D, shs, colors_precomp,
+                         alphas, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx,
+                         tanfovy, radii, geom_buf, binning_buf, image_buf, dL_dout_color, dL_dout_depth, dL_dout_alpha, scratch,
+                         dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, stream);
+}
+
+int htgs_backward_raw(int P, int D, int64_t R, int W, int H, const float* background, const float* xyz,
+                      const float* features_dc, const float* features_rest, const float* alphas, const float* scaling_raw,
+                      float scale_modifier, const float* rotation_raw, const float* opacity_raw, const float* viewmatrix,
+                      const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int* radii,
+                      const void* geom_buf, const void* binning_buf, const void* image_buf, const float* dL_dout_color,
+                      const float* dL_dout_depth, const float* dL_dout_alpha, void* scratch, float* dL_dmeans2D,
+                      float* dL_dxyz, float* dL_dfeatures_dc, float* dL_dfeatures_rest, float* dL_dopacity_raw,
+                      float* dL_dscaling_raw, float* dL_drotation_raw, void* stream) {
+    const char* who = "htgs_backward_raw";
+    if (P <= 0) return 0;
+    if (!features_dc || !features_rest || !scaling_raw || !rotation_raw || !opacity_raw || !dL_dfeatures_dc ||
+        !dL_dfeatures_rest || !dL_dopacity_raw || !dL_dscaling_raw || !dL_drotation_raw) {
+        set_error("%s: null parameter / gradient pointer", who);
+        return 1;
+    }
+    if ((reinterpret_cast<size_t>(features_rest) & 15) || (reinterpret_cast<size_t>(dL_dfeatures_rest) & 15)) {
+        set_error("%s: features_rest and its gradient must be 16-byte aligned", who);
+        return 1;
+    }
+    return backward_impl(who, features_rest, opacity_raw, dL_dfeatures_rest, P, D, 16, R, W, H, background, xyz, features_dc,
+                         nullptr, alphas, scaling_raw, scale_modifier, rotation_raw, nullptr, viewmatrix, projmatrix, campos,
+                         tanfovx, tanfovy, radii, geom_buf, binning_buf, image_buf, dL_dout_color, dL_dout_depth, dL_dout_alpha,
+                         scratch, dL_dmeans2D, dL_dopacity_raw, nullptr, dL_dxyz, nullptr, dL_dfeatures_dc, dL_dscaling_raw,
+                         dL_drotation_raw, stream);
 }
 
 int htgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,

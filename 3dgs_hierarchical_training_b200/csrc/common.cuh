@@ -63,10 +63,10 @@ ImgView img_view(void* base, int W, int H);
 
 // ---- kernels' host launchers (one per .cu) ---------------------------------
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
-                      const float* rotations, const float* opacities, const float* shs, const float* cov3D_precomp,
-                      const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
-                      const float* campos, int W, int H, float tanfovx, float tanfovy, int prefiltered,
-                      const GeomView& g, int* radii, cudaStream_t st);
+                      const float* rotations, const float* opacities, const float* shs, const float* shs_rest,
+                      const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                      const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                      int prefiltered, const GeomView& g, int* radii, cudaStream_t st);
 int launch_scan_block_sums(int P, const GeomView& g, cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t st);
 int launch_make_keys(int P, int W, int H, const int* radii, const GeomView& g, uint64_t* keys, uint32_t* values,
@@ -82,7 +82,7 @@ int launch_blend_backward(int P, int W, int H, const uint2* ranges, const uint32
                           const float* bg, const float* alphas, const uint32_t* n_contrib, const float* dL_dpix,
                           const float* dL_ddepth, const float* dL_dalpha, float* gacc, cudaStream_t st);
 int launch_geom_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
-                         const float* colors_precomp, const float* scales, float scale_modifier,
+                         const float* shs_rest, const float* opacity_raw, float* dL_dsh_rest, const float* colors_precomp, const float* scales, float scale_modifier,
                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
                          const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
                          const GeomView& g, const float* gacc, float* dL_dmeans2D, float* dL_dopacity,

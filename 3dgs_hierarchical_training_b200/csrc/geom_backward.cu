@@ -9,7 +9,7 @@
 // recomputes cov3D / T instead of loading stored copies, and writes EVERY output
 // element exactly once (zeros for culled Gaussians), so the caller allocates the
 // outputs uninitialised and no memset pass over 300 B/Gaussian is needed.
-#include "gs_math.cuh"
+#include "raw_params.cuh"
 
 namespace htgs {
 
@@ -31,9 +31,15 @@ __device__ __forceinline__ void write_sh_grad(float* __restrict__ out, const flo
     for (int e = 48; e < 3 * M; e++) out[e] = 0.f;
 }
 
+// RAW = true (raw_params.cuh): `scales`, `rotations` are un-activated, `shs` / `dL_dsh` are _features_dc and
+// its gradient, `shs_rest` / `dL_dsh_rest` are _features_rest and its gradient, `opacity_raw` the
+// un-activated opacity; all parameter gradients are written with respect to the raw parameters.
+template <bool RAW>
 __global__ void __launch_bounds__(256)
 geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
-                     const float* __restrict__ shs, const uint8_t* __restrict__ clamped, bool colors_are_precomp,
+                     const float* __restrict__ shs, const float* __restrict__ shs_rest,
+                     const float* __restrict__ opacity_raw, float* __restrict__ dL_dsh_rest,
+                     const uint8_t* __restrict__ clamped, bool colors_are_precomp,
                      const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
                      const float* __restrict__ cov3D_precomp, const float* __restrict__ viewmatrix,
                      const float* __restrict__ projmatrix, const float* __restrict__ campos, float h_x, float h_y,
@@ -61,7 +67,13 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
 #pragma unroll
             for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = 0.f;
         }
-        if (dL_dsh) {
+        if (RAW) {
+            store3(dL_dsh + 3 * (size_t)idx, 0.f, 0.f, 0.f);
+            float z45[RAW_REST];
+#pragma unroll
+            for (int k = 0; k < RAW_REST; k++) z45[k] = 0.f;
+            store_rest_row(dL_dsh_rest, idx, z45);
+        } else if (dL_dsh) {
             float* o = dL_dsh + (size_t)idx * M * 3;
             if (sh_vec) {
                 for (int i = 0; i < M * 3 / 4; i++) reinterpret_cast<float4*>(o)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -84,7 +96,8 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
 
     // ---- covariance: recompute what the forward used ----
     float c3[6];
-    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f), q_raw = q;
+    float q_norm = 1.f;
     float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
     if (cov3D_precomp != nullptr) {
 #pragma unroll
@@ -92,6 +105,11 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
     } else {
         q = reinterpret_cast<const float4*>(rotations)[idx];
         sc0 = scales[3 * (size_t)idx]; sc1 = scales[3 * (size_t)idx + 1]; sc2 = scales[3 * (size_t)idx + 2];
+        if (RAW) {
+            q_raw = q;
+            q = act_rotation(q, q_norm);
+            sc0 = act_scale(sc0); sc1 = act_scale(sc1); sc2 = act_scale(sc2);
+        }
         cov3d_from_scale_rot(sc0, sc1, sc2, scale_modifier, q, c3);
     }
 
@@ -172,8 +190,16 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
 #pragma unroll
         for (int k = 0; k < 16; k++) sd[k] = 0.f;
         const int nact = (D + 1) * (D + 1);
-        const bool fast = (M == 16) && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0);
-        if (fast) {
+        const bool fast = !RAW && (M == 16) && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0);
+        if (RAW) {
+            float e[RAW_REST];
+#pragma unroll
+            for (int k = 0; k < RAW_REST; k++) e[k] = 0.f;
+            if (D > 0) load_rest_row(shs_rest, idx, 3 * nact - 3, e);
+            sd[0] = __ldg(shs + 3 * (size_t)idx) * r0 + __ldg(shs + 3 * (size_t)idx + 1) * r1 + __ldg(shs + 3 * (size_t)idx + 2) * r2;
+#pragma unroll
+            for (int k = 1; k < 16; k++) sd[k] = e[3 * k - 3] * r0 + e[3 * k - 2] * r1 + e[3 * k - 1] * r2;
+        } else if (fast) {
             const float4* sh4 = reinterpret_cast<const float4*>(sh);
 #pragma unroll
             for (int i = 0; i < 12; i++) {
@@ -236,7 +262,19 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
         }
 #undef SHDOT
         float* o = dL_dsh + (size_t)idx * M * 3;
-        if (fast && sh_vec) {
+        if (RAW) {
+#pragma unroll
+            for (int k = 1; k < 16; k++)
+                if (k >= ncoef) w[k] = 0.f;
+            store3(dL_dsh + 3 * (size_t)idx, w[0] * r0, w[0] * r1, w[0] * r2);
+            float e[RAW_REST];
+#pragma unroll
+            for (int k = 0; k < RAW_REST; k++) {
+                const int c = k % 3;
+                e[k] = w[1 + k / 3] * (c == 0 ? r0 : (c == 1 ? r1 : r2));
+            }
+            store_rest_row(dL_dsh_rest, idx, e);
+        } else if (fast && sh_vec) {
             // twelve 128-bit stores; coefficient and channel of every element are compile-time
 #pragma unroll
             for (int k = 1; k < 16; k++)
@@ -298,12 +336,25 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
                4 * y * (dMt[2][2] + dMt[0][0]);
         dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) -
                4 * z * (dMt[1][1] + dMt[0][0]);
+        if (RAW) {
+            // exp backward; F.normalize backward: (g - qhat (qhat . g)) / n
+            dsc[0] *= sc0; dsc[1] *= sc1; dsc[2] *= sc2;
+            const float dot = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
+            const float inv_n = 1.0f / q_norm;
+            dq = make_float4((dq.x - q.x * dot) * inv_n, (dq.y - q.y * dot) * inv_n, (dq.z - q.z * dot) * inv_n,
+                             (dq.w - q.w * dot) * inv_n);
+            (void)q_raw;
+        }
         store3(dL_dscales + 3 * (size_t)idx, dsc[0], dsc[1], dsc[2]);
         reinterpret_cast<float4*>(dL_drotations)[idx] = dq;
     }
 
     store3(dL_dmeans2D + 3 * (size_t)idx, g2x, g2y, 0.f);
-    dL_dopacity[idx] = g_opacity;
+    if (RAW) {
+        const float sg = act_opacity(opacity_raw[idx]);
+        dL_dopacity[idx] = g_opacity * sg * (1.0f - sg);  // sigmoid backward
+    } else
+        dL_dopacity[idx] = g_opacity;
     store3(dL_dmeans3D + 3 * (size_t)idx, dmx, dmy, dmz);
     if (dL_dcolors) {
         if (colors_are_precomp) store3(dL_dcolors + 3 * (size_t)idx, gc0, gc1, gc2);
@@ -316,18 +367,23 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
 }
 
 int launch_geom_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
-                         const float* colors_precomp, const float* scales, float scale_modifier,
+                         const float* shs_rest, const float* opacity_raw, float* dL_dsh_rest, const float* colors_precomp, const float* scales, float scale_modifier,
                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
                          const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
                          const GeomView& g, const float* gacc, float* dL_dmeans2D, float* dL_dopacity,
                          float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
                          float* dL_drotations, cudaStream_t st) {
     const float h_y = H / (2.0f * tanfovy), h_x = W / (2.0f * tanfovx);  // rasterizer_impl.cu:387-388
-    geom_backward_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, D, M, means3D, radii, shs, g.clamped, colors_precomp != nullptr,
-                                                          scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
-                                                          projmatrix, campos, h_x, h_y, tanfovx, tanfovy, gacc,
-                                                          dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D,
-                                                          dL_dsh, dL_dscales, dL_drotations);
+    if (shs_rest != nullptr)  // raw-parameter entry point
+        geom_backward_kernel<true><<<(P + 255) / 256, 256, 0, st>>>(
+            P, D, M, means3D, radii, shs, shs_rest, opacity_raw, dL_dsh_rest, g.clamped, false, scales, scale_modifier,
+            rotations, cov3D_precomp, viewmatrix, projmatrix, campos, h_x, h_y, tanfovx, tanfovy, gacc, dL_dmeans2D,
+            dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+    else
+        geom_backward_kernel<false><<<(P + 255) / 256, 256, 0, st>>>(
+            P, D, M, means3D, radii, shs, nullptr, nullptr, nullptr, g.clamped, colors_precomp != nullptr, scales,
+            scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, h_x, h_y, tanfovx, tanfovy, gacc,
+            dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
     HTGS_LAUNCH_CHECK("geom_backward_kernel");
     return 0;
 }

@@ -8,7 +8,7 @@
 // survive culling; cov3D is not stored (backward recomputes it bit-identically
 // from scale/rotation), colour and depth are packed into one float4 so the
 // blend kernels gather 40 B per instance.
-#include "gs_math.cuh"
+#include "raw_params.cuh"
 #include <cstdio>
 
 namespace htgs {
@@ -92,10 +92,14 @@ __device__ __forceinline__ void load_sh_and_eval(const float* __restrict__ shp, 
     sh_to_rgb<D>(sh, x, y, z, res);
 }
 
+// RAW = true: `scales`, `rotations`, `opacities` are the un-activated parameters, `shs` is _features_dc
+// [P,1,3] and `shs_rest` is _features_rest [P,15,3] (raw_params.cuh); M is 16.
+template <bool RAW>
 __global__ void __launch_bounds__(HTGS_PRE_BLOCK)
 preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
                   float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
-                  const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
+                  const float* __restrict__ shs, const float* __restrict__ shs_rest,
+                  const float* __restrict__ cov3D_precomp,
                   const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
                   const float* __restrict__ projmatrix, const float* __restrict__ campos, int W, int H,
                   float tanfovx, float tanfovy, float focal_x, float focal_y, int gx, int gy, int prefiltered,
@@ -136,8 +140,14 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
 #pragma unroll
                 for (int k = 0; k < 6; k++) cov3[k] = cov3D_precomp[6 * (size_t)idx + k];
             } else {
-                const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-                cov3d_from_scale_rot(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2], scale_modifier, q, cov3);
+                float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+                float s0 = scales[3 * idx], s1 = scales[3 * idx + 1], s2 = scales[3 * idx + 2];
+                if (RAW) {
+                    float n;
+                    q = act_rotation(q, n);
+                    s0 = act_scale(s0); s1 = act_scale(s1); s2 = act_scale(s2);
+                }
+                cov3d_from_scale_rot(s0, s1, s2, scale_modifier, q, cov3);
             }
             const Ewa e = ewa_setup(px, py, pz, vm, focal_x, focal_y, tanfovx, tanfovy);
             float a, b, c;
@@ -162,14 +172,31 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
                 const float dx = SB(px, s_cam[32]), dy = SB(py, s_cam[33]), dz = SB(pz, s_cam[34]);
                 const float len = __fsqrt_rn(FM(dz, dz, FM(dx, dx, MU(dy, dy))));
                 const float x = DV(dx, len), y = DV(dy, len), z = DV(dz, len);
+                float res[3];
+                if (RAW) {
+                    float sh[48];
+                    sh[0] = __ldg(shs + 3 * (size_t)idx); sh[1] = __ldg(shs + 3 * (size_t)idx + 1); sh[2] = __ldg(shs + 3 * (size_t)idx + 2);
+                    float e[RAW_REST];
+#pragma unroll
+                    for (int k = 0; k < RAW_REST; k++) e[k] = 0.f;
+                    if (D > 0) load_rest_row(shs_rest, idx, 3 * (D + 1) * (D + 1) - 3, e);
+#pragma unroll
+                    for (int k = 0; k < RAW_REST; k++) sh[3 + k] = e[k];
+                    switch (D) {
+                        case 0: sh_to_rgb<0>(sh, x, y, z, res); break;
+                        case 1: sh_to_rgb<1>(sh, x, y, z, res); break;
+                        case 2: sh_to_rgb<2>(sh, x, y, z, res); break;
+                        default: sh_to_rgb<3>(sh, x, y, z, res); break;
+                    }
+                } else {
                 const float* shp = shs + (size_t)idx * M * 3;
                 const bool vec_ok = ((M * 3) % 4 == 0) && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0);
-                float res[3];
                 switch (D) {
                     case 0: load_sh_and_eval<0>(shp, vec_ok && M * 3 >= 4, x, y, z, res); break;
                     case 1: load_sh_and_eval<1>(shp, vec_ok, x, y, z, res); break;
                     case 2: load_sh_and_eval<2>(shp, vec_ok && M * 3 >= 28, x, y, z, res); break;
                     default: load_sh_and_eval<3>(shp, vec_ok, x, y, z, res); break;
+                }
                 }
 #pragma unroll
                 for (int ch = 0; ch < 3; ch++) {
@@ -183,7 +210,7 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
                 rgb[2] = colors_precomp[3 * (size_t)idx + 2];
             }
             means2D[idx] = make_float2(pix_x, pix_y);
-            conic_opacity[idx] = make_float4(conx, cony, conz, opacities[idx]);
+            conic_opacity[idx] = make_float4(conx, cony, conz, RAW ? act_opacity(opacities[idx]) : opacities[idx]);
             feat[idx] = make_float4(rgb[0], rgb[1], rgb[2], depth);
             my_tiles = nt;
             my_radius = rad;
@@ -258,7 +285,8 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 }
 
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
-                      const float* rotations, const float* opacities, const float* shs, const float* cov3D_precomp,
+                      const float* rotations, const float* opacities, const float* shs, const float* shs_rest,
+                      const float* cov3D_precomp,
                       const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
                       const float* campos, int W, int H, float tanfovx, float tanfovy, int prefiltered,
                       const GeomView& g, int* radii, cudaStream_t st) {
@@ -266,11 +294,18 @@ int launch_preprocess(int P, int D, int M, const float* means3D, const float* sc
     const float focal_x = W / (2.0f * tanfovx);
     const int gx = (W + HTGS_TILE - 1) / HTGS_TILE, gy = (H + HTGS_TILE - 1) / HTGS_TILE;
     const int nb = (P + HTGS_PRE_BLOCK - 1) / HTGS_PRE_BLOCK;
-    preprocess_kernel<<<nb, HTGS_PRE_BLOCK, 0, st>>>(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
-                                                     cov3D_precomp, colors_precomp, viewmatrix, projmatrix, campos, W, H,
-                                                     tanfovx, tanfovy, focal_x, focal_y, gx, gy, prefiltered, radii,
-                                                     g.means2D, g.conic_opacity, g.feat, g.clamped, g.tiles_touched,
-                                                     g.block_sums);
+    if (shs_rest != nullptr)  // raw-parameter entry point
+        preprocess_kernel<true><<<nb, HTGS_PRE_BLOCK, 0, st>>>(P, D, M, means3D, scales, scale_modifier, rotations, opacities,
+                                                               shs, shs_rest, cov3D_precomp, colors_precomp, viewmatrix,
+                                                               projmatrix, campos, W, H, tanfovx, tanfovy, focal_x, focal_y,
+                                                               gx, gy, prefiltered, radii, g.means2D, g.conic_opacity, g.feat,
+                                                               g.clamped, g.tiles_touched, g.block_sums);
+    else
+        preprocess_kernel<false><<<nb, HTGS_PRE_BLOCK, 0, st>>>(P, D, M, means3D, scales, scale_modifier, rotations, opacities,
+                                                                shs, nullptr, cov3D_precomp, colors_precomp, viewmatrix,
+                                                                projmatrix, campos, W, H, tanfovx, tanfovy, focal_x, focal_y,
+                                                                gx, gy, prefiltered, radii, g.means2D, g.conic_opacity, g.feat,
+                                                                g.clamped, g.tiles_touched, g.block_sums);
     HTGS_LAUNCH_CHECK("preprocess_kernel");
     return 0;
 }

@@ -42,6 +42,17 @@ _SIGNATURES = {
                               c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float,
                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    # (P, D, xyz, scaling_raw, scale_modifier, rotation_raw, opacity_raw, features_dc, features_rest, view, proj, campos,
+    #  W, H, tanfovx, tanfovy, prefiltered, geom, radii, pinned_count, stream)
+    "htgs_forward_preprocess_raw_async": (c_int, [c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+                                                  c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,
+                                                  c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    # (P, D, R, W, H, bg, xyz, f_dc, f_rest, alphas, scaling_raw, scale_modifier, rotation_raw, opacity_raw, view, proj,
+    #  campos, tanfovx, tanfovy, radii, geom, binning, image, dL_dcolor, dL_ddepth, dL_dalpha, scratch, 7 gradient outputs, stream)
+    "htgs_backward_raw": (c_int, [c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_mark_visible": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_sort_scratch_bytes": (c_size_t, [c_int64]),
     "htgs_sort_pairs": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -218,6 +218,36 @@ int htgs_densification_stats(int P, const int* radii, const float* grad_means2D,
 int htgs_adam_step(int n_groups, const htgs_adam_group* groups, float beta1, float beta2, float eps,
                    long long step, void* stream);
 
+/* ---- un-activated, un-concatenated parameters (opt-in) ----
+ * The HT model stores _scaling, _rotation, _opacity, _features_dc [P,1,3] and _features_rest [P,15,3]
+ * and every render call first materialises exp / F.normalize / sigmoid / torch.cat of them
+ * (scene/gaussian_model_ht.py:127-188, call site :834-866); autograd then walks back through the same
+ * four ops.  These two entry points take the stored parameters as they are, apply the activations in
+ * registers inside K1 / K7 and return gradients with respect to the STORED parameters, so neither the
+ * activated tensors nor the 192 B/Gaussian concatenated SH tensor (nor the split of its gradient) ever
+ * exist.  M is fixed at 16 (degree-3 storage); D <= 3 is the active degree.  features_rest and
+ * dL_dfeatures_rest must be 16-byte aligned.  Pair with htgs_forward_render / _capacity unchanged.
+ *   forward : identical outputs to htgs_forward_preprocess_async fed with the activated tensors.
+ *   backward: dL_dscaling_raw = dL_dscales * exp(_scaling); dL_drotation_raw = normalize-backward of
+ *             dL_drotations; dL_dopacity_raw = dL_dopacity * s(1-s); dL_dfeatures_dc / _rest = the two
+ *             slices of dL_dsh. */
+int htgs_forward_preprocess_raw_async(int P, int D, const float* xyz, const float* scaling_raw, float scale_modifier,
+                                      const float* rotation_raw, const float* opacity_raw,
+                                      const float* features_dc, const float* features_rest,
+                                      const float* viewmatrix, const float* projmatrix, const float* campos,
+                                      int W, int H, float tanfovx, float tanfovy, int prefiltered,
+                                      void* geom_buf, int* radii, uint32_t* num_rendered_pinned_host, void* stream);
+int htgs_backward_raw(int P, int D, int64_t R, int W, int H, const float* background, const float* xyz,
+                      const float* features_dc, const float* features_rest, const float* alphas,
+                      const float* scaling_raw, float scale_modifier, const float* rotation_raw,
+                      const float* opacity_raw, const float* viewmatrix, const float* projmatrix,
+                      const float* campos, float tanfovx, float tanfovy, const int* radii,
+                      const void* geom_buf, const void* binning_buf, const void* image_buf,
+                      const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+                      void* scratch, float* dL_dmeans2D, float* dL_dxyz, float* dL_dfeatures_dc,
+                      float* dL_dfeatures_rest, float* dL_dopacity_raw, float* dL_dscaling_raw,
+                      float* dL_drotation_raw, void* stream);
+
 /* ---- image loss (opt-in) ----
  * loss = (1 - lambda) * mean|pred - gt| + lambda * (1 - SSIM(pred, gt)), the training loss of
  * trainer/losses.py:98-136 (SSIM: 11x11 sigma-1.5 window, zero padding, per channel, :147-200), for
