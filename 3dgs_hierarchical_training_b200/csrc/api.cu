@@ -124,7 +124,7 @@ int htgs_blend_stats(int P, int64_t R, int W, int H, const void* geom_buf, const
     GeomView g = geom_view(const_cast<void*>(geom_buf), P);
     ImgView img = img_view(const_cast<void*>(image_buf), W, H);
     BinView b = bin_view(const_cast<void*>(binning_buf), R, W, H);
-    HTGS_CUDA_CHECK(cudaMemsetAsync(stats3, 0, 3 * sizeof(unsigned long long), st));
+    HTGS_CUDA_CHECK(cudaMemsetAsync(stats3, 0, HTGS_BLEND_NSTATS * sizeof(unsigned long long), st));
     return launch_blend_stats(W, H, img.ranges, b.values_sorted, g, stats3, st);
 }
 const char* htgs_last_error(void) { return g_error; }

@@ -44,6 +44,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, dsum = 0.f;
     uint32_t last_contributor = 0;
     uint32_t st_blended = 0, st_tested = 0, st_done_pos = 0;
+    uint32_t st_hist[7] = {0, 0, 0, 0, 0, 0, 0};  // warp visits by number of blending lanes: 0, 1, 2-4, 5-8, 9-16, 17-24, 25-32
 
     for (int base = 0; base < n; base += FWD_BATCH) {
         // leave when every pixel of the tile is saturated (forward.cu:313-315)
@@ -82,6 +83,12 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     done = 1;
                     if (STATS) st_done_pos = chunk_pos + (uint32_t)b;
                 }
+                if (STATS) {
+                    const int nl = __popc(__ballot_sync(0xffffffffu, live && !kill));
+                    const int bucket = nl == 0 ? 0 : nl == 1 ? 1 : nl <= 4 ? 2 : nl <= 8 ? 3 : nl <= 16 ? 4 : nl <= 24 ? 5 : 6;
+#pragma unroll
+                    for (int k = 0; k < 7; k++) st_hist[k] += (k == bucket) ? 1u : 0u;
+                }
                 if (live && !kill) {
                     const float2 q2 = lds64(a + 32);  // b, depth
                     C0 = FM(T, MU(alpha, q1.z), C0);
@@ -102,6 +109,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             atomicAdd(&stats[0], (unsigned long long)(st_done_pos ? st_done_pos : (uint32_t)n));
             atomicAdd(&stats[1], (unsigned long long)st_blended);
             atomicAdd(&stats[2], (unsigned long long)st_tested);
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < 7; k++) atomicAdd(&stats[3 + k], (unsigned long long)st_hist[k]);
         }
         return;
     }

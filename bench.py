@@ -295,10 +295,12 @@ def run_ours(args, rank, world, local_rank):
             bg, params["means3D"], empty, params["opacities"], params["scales"], params["rotations"], 1.0, empty,
             cam_d["viewmatrix"], cam_d["projmatrix"], cam_d["tanfovx"], cam_d["tanfovy"], H, W, params["shs"], 3,
             cam_d["campos"], False, False)
-        stats = torch.zeros(3, dtype=torch.int64, device=dev)
+        stats = torch.zeros(10, dtype=torch.int64, device=dev)  # HTGS_BLEND_NSTATS
         nat.check(lib.htgs_blend_stats(P, R, W, H, geom.data_ptr(), nat.ptr(binning), img.data_ptr(), stats.data_ptr(),
                                        ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "htgs_blend_stats")
-        n_ref_tested, n_blended, n_ours_tested = [int(x) for x in stats.cpu()]
+        stats_h = [int(x) for x in stats.cpu()]
+        n_ref_tested, n_blended, n_ours_tested = stats_h[:3]
+        visit_hist = dict(zip(("0", "1", "2-4", "5-8", "9-16", "17-24", "25-32"), stats_h[3:10]))
         P_vis = int((radii > 0).sum())
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     key_bits = 32 + max(1, (tiles).bit_length())
@@ -337,6 +339,7 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": args.workload, "P": P, "W": W, "H": H, "sh_degree": 3, "views_per_step_per_gpu": len(cams_d), "views_per_step": batch_views,
                    "P_visible": P_vis, "R_instances": int(R), "pairs_tested_reference_loop": n_ref_tested,
                    "pairs_tested_after_culling": n_ours_tested, "pairs_blended": n_blended,
+                   "warp_visits_by_blending_lanes": visit_hist,
                    "l2": "inputs+outputs per step (~0.7 GB) exceed the 126 MB L2; no explicit flush",
                    "parallelism": f"view-parallel dp{world}" + (" + NCCL all-reduce of 59 f32/Gaussian" if world > 1 else "")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * len(cams_d) * (5 + passes + 2 + 2),

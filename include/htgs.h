@@ -187,14 +187,16 @@ int htgs_sort_pairs_static(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* 
  * caller's stream around each stage; htgs_profile_read() waits for them, returns the summed
  * milliseconds and launch counts per stage (order: preprocess, scan, make_keys, sort, tile_ranges,
  * blend_fwd, zero_acc, blend_bwd, geom_bwd) and clears the log.  Process-wide, not thread-safe.
- * htgs_blend_stats() re-walks the tile lists of the last forward and writes three counters to
- * stats3 (device, 3 x uint64): pair tests of the reference's per-pixel loop, blended pairs, pair
- * tests this library executes after reach-mask culling. */
+ * htgs_blend_stats() re-walks the tile lists of the last forward and writes HTGS_BLEND_NSTATS counters
+ * to stats (device, uint64 each): [0] pair tests of the reference's per-pixel loop, [1] blended pairs,
+ * [2] pair tests this library executes after reach-mask culling, [3..9] number of (warp, Gaussian)
+ * visits in which 0, 1, 2-4, 5-8, 9-16, 17-24, 25-32 of the warp's 32 pixels blended the Gaussian. */
+#define HTGS_BLEND_NSTATS 10
 #define HTGS_NUM_STAGES 9
 void htgs_profile_enable(int on);
 int htgs_profile_read(double* ms_sum, int* counts, int cap);
 int htgs_blend_stats(int P, int64_t R, int W, int H, const void* geom_buf, const void* binning_buf,
-                     const void* image_buf, unsigned long long* stats3, void* stream);
+                     const void* image_buf, unsigned long long* stats, void* stream);
 
 /* ---- per-step tail after the backward (opt-in, outside the plugin surface) ----
  * htgs_densification_stats replaces the three boolean-mask updates of
