@@ -18,6 +18,13 @@ class AdamGroup(ctypes.Structure):
                 ("numel", ctypes.c_longlong), ("lr", c_float)]
 
 
+class RowTensor(ctypes.Structure):
+    """htgs_row_tensor of include/htgs.h."""
+    _fields_ = [("src", c_void_p), ("dst", c_void_p), ("row_words", c_int), ("zero_new", c_int)]
+
+
+ROWS_MAX_TENSORS = 24  # HTGS_ROWS_MAX_TENSORS
+
 _SIGNATURES = {
     "htgs_abi_version": (c_int, []),
     "htgs_last_error": (ctypes.c_char_p, []),
@@ -54,6 +61,10 @@ _SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_mark_visible": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_row_scan_scratch_bytes": (c_size_t, [c_int]),
+    "htgs_row_scan": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_rows_compact": (c_int, [c_int, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),
+    "htgs_rows_append": (c_int, [c_int, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),
     "htgs_sort_scratch_bytes": (c_size_t, [c_int64]),
     "htgs_sort_pairs": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_sort_pairs_static": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -82,3 +82,124 @@ class FusedAdam(torch.optim.Optimizer):
                     nat.check(lib.htgs_adam_step(len(chunk), arr, float(betas[0]), float(betas[1]), float(eps), step, _stream(dev)),
                               "htgs_adam_step")
         return loss
+
+
+# ---- row surgery for prune / clone (first half) ----
+
+def _move_rows(mask, tensors, append, zero_new=None):
+    """Shared driver: one mask scan, one host read of the selected count, one launch per <= 24 tensors."""
+    if mask.dtype not in (torch.bool, torch.uint8) or not mask.is_cuda or mask.dim() != 1:
+        raise RuntimeError("row mask must be a 1-D bool/uint8 CUDA tensor")
+    P = int(mask.numel())
+    dev = mask.device
+    mask = mask.contiguous()
+    srcs = []
+    for t in tensors:
+        if not t.is_cuda or t.device != dev:
+            raise RuntimeError("row tensors must live on the mask's CUDA device")
+        if t.size(0) != P:
+            raise RuntimeError(f"row tensor has {t.size(0)} rows, mask has {P}")
+        if t.element_size() != 4:
+            raise RuntimeError("row tensors must have 4-byte elements")
+        srcs.append(t.detach().contiguous())
+    lib = nat.lib()
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        scratch = torch.empty(lib.htgs_row_scan_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        pinned = torch.zeros(1, dtype=torch.int32).pin_memory()
+        nat.check(lib.htgs_row_scan(P, mask.data_ptr(), scratch.data_ptr(), pinned.data_ptr(), st), "htgs_row_scan")
+        torch.cuda.current_stream(dev).synchronize()  # the one host read: output sizes depend on it
+        count = int(pinned[0]) & 0xFFFFFFFF
+        n_out = P + count if append else count
+        outs = [torch.empty((n_out,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev) for t in srcs]
+        fn, name = (lib.htgs_rows_append, "htgs_rows_append") if append else (lib.htgs_rows_compact, "htgs_rows_compact")
+        for lo in range(0, len(srcs), nat.ROWS_MAX_TENSORS):
+            part = [(k, srcs[k]) for k in range(lo, min(lo + nat.ROWS_MAX_TENSORS, len(srcs))) if srcs[k].numel() > 0]
+            if not part or P == 0 or n_out == 0:
+                continue
+            arr = (nat.RowTensor * len(part))()
+            for j, (k, t) in enumerate(part):
+                arr[j] = nat.RowTensor(t.data_ptr(), outs[k].data_ptr(), t.numel() // P, int(bool(zero_new[k])) if zero_new else 0)
+            nat.check(fn(P, mask.data_ptr(), scratch.data_ptr(), len(part), arr, st), name)
+    return outs, count
+
+
+def select_rows(mask, tensors):
+    """[t[mask] for t in tensors] with one scan, one sync and one launch (torch: a nonzero + sync + gather each)."""
+    return _move_rows(mask, tensors, append=False)[0]
+
+
+def append_selected_rows(mask, tensors, zero_new=None):
+    """[torch.cat((t, t[mask])) for t in tensors]; where zero_new[k] is true the appended rows are zeros instead."""
+    return _move_rows(mask, tensors, append=True, zero_new=zero_new)[0]
+
+
+def prune_optimizer(optimizer, keep_mask, extra=()):
+    """`_prune_optimizer` (scene/gaussian_model_ht.py:548-566) for every group at once, plus `extra` tensors
+    (xyz_gradient_accum, denom, max_radii2D of prune_points :568-583) in the same launch.
+    Returns ({group name: new nn.Parameter}, [pruned extra tensors])."""
+    groups = [g for g in optimizer.param_groups]
+    tensors, slots = [], []
+    for gi, g in enumerate(groups):
+        if len(g["params"]) != 1:
+            raise RuntimeError("prune_optimizer expects one parameter per group (the reference's layout)")
+        p = g["params"][0]
+        tensors.append(p.data)
+        slots.append((gi, "param"))
+        st = optimizer.state.get(p, None)
+        if st is not None and "exp_avg" in st:
+            tensors += [st["exp_avg"], st["exp_avg_sq"]]
+            slots += [(gi, "exp_avg"), (gi, "exp_avg_sq")]
+    n_opt = len(tensors)
+    outs = select_rows(keep_mask, tensors + list(extra))
+    new_params = {}
+    by_group = {}
+    for (gi, what), t in zip(slots, outs[:n_opt]):
+        by_group.setdefault(gi, {})[what] = t
+    for gi, g in enumerate(groups):
+        old = g["params"][0]
+        stored = optimizer.state.get(old, None)
+        newp = torch.nn.Parameter(by_group[gi]["param"].requires_grad_(True))
+        if stored is not None:
+            if "exp_avg" in by_group[gi]:
+                stored["exp_avg"], stored["exp_avg_sq"] = by_group[gi]["exp_avg"], by_group[gi]["exp_avg_sq"]
+            del optimizer.state[old]
+            optimizer.state[newp] = stored
+        g["params"][0] = newp
+        new_params[g.get("name", str(gi))] = newp
+    return new_params, outs[n_opt:]
+
+
+def clone_selected_to_optimizer(optimizer, selected_mask):
+    """densify_and_clone's tensor work (scene/gaussian_model_ht.py:656-672 + cat_tensors_to_optimizer :585-611):
+    every parameter gets its selected rows appended, both Adam moments get as many zero rows.
+    Returns {group name: new nn.Parameter}."""
+    groups = [g for g in optimizer.param_groups]
+    tensors, zero_new, slots = [], [], []
+    for gi, g in enumerate(groups):
+        if len(g["params"]) != 1:
+            raise RuntimeError("clone_selected_to_optimizer expects one parameter per group")
+        p = g["params"][0]
+        tensors.append(p.data); zero_new.append(False); slots.append((gi, "param"))
+        st = optimizer.state.get(p, None)
+        if st is not None and "exp_avg" in st:
+            tensors += [st["exp_avg"], st["exp_avg_sq"]]
+            zero_new += [True, True]
+            slots += [(gi, "exp_avg"), (gi, "exp_avg_sq")]
+    outs = append_selected_rows(selected_mask, tensors, zero_new)
+    by_group = {}
+    for (gi, what), t in zip(slots, outs):
+        by_group.setdefault(gi, {})[what] = t
+    new_params = {}
+    for gi, g in enumerate(groups):
+        old = g["params"][0]
+        stored = optimizer.state.get(old, None)
+        newp = torch.nn.Parameter(by_group[gi]["param"].requires_grad_(True))
+        if stored is not None:
+            if "exp_avg" in by_group[gi]:
+                stored["exp_avg"], stored["exp_avg_sq"] = by_group[gi]["exp_avg"], by_group[gi]["exp_avg_sq"]
+            del optimizer.state[old]
+            optimizer.state[newp] = stored
+        g["params"][0] = newp
+        new_params[g.get("name", str(gi))] = newp
+    return new_params

@@ -220,6 +220,30 @@ int htgs_densification_stats(int P, const int* radii, const float* grad_means2D,
 int htgs_adam_step(int n_groups, const htgs_adam_group* groups, float beta1, float beta2, float eps,
                    long long step, void* stream);
 
+/* ---- row surgery for prune / clone (first half; opt-in) ----
+ * Replaces the per-tensor boolean-mask indexing of _prune_optimizer / prune_points and the per-tensor
+ * torch.cat of cat_tensors_to_optimizer / densification_postfix in the clone case
+ * (scene/gaussian_model_ht.py:548-616, :656-672): scan the mask once, then move the rows of up to
+ * HTGS_ROWS_MAX_TENSORS float32 tensors in one launch.
+ *   htgs_row_scan      offsets[i] = number of non-zero mask entries before i (kept in scratch); the total
+ *                      is copied asynchronously to *count_pinned_host (pinned host memory, valid once the
+ *                      stream reached this point) so the caller can size the outputs.
+ *   htgs_rows_compact  dst[offsets[i]] = src[i] where mask[i] != 0          == torch src[mask]
+ *   htgs_rows_append   dst[0:P] = src; dst[P + offsets[i]] = src[i] (or 0 when zero_new) where mask[i] != 0
+ *                                                                            == torch.cat((src, src[mask])) / cat((src, zeros))
+ * mask: uint8/bool [P]; every tensor is [P, row_words] 32-bit words, contiguous; dst sized by the caller. */
+#define HTGS_ROWS_MAX_TENSORS 24
+typedef struct {
+    const void* src;
+    void* dst;
+    int row_words; /* 32-bit words per row */
+    int zero_new;  /* htgs_rows_append only: appended rows are zero (Adam moments of cloned Gaussians) */
+} htgs_row_tensor;
+size_t htgs_row_scan_scratch_bytes(int P);
+int htgs_row_scan(int P, const uint8_t* mask, void* scratch, uint32_t* count_pinned_host, void* stream);
+int htgs_rows_compact(int P, const uint8_t* mask, const void* scratch, int n_tensors, const htgs_row_tensor* tensors, void* stream);
+int htgs_rows_append(int P, const uint8_t* mask, const void* scratch, int n_tensors, const htgs_row_tensor* tensors, void* stream);
+
 /* ---- un-activated, un-concatenated parameters (opt-in) ----
  * The HT model stores _scaling, _rotation, _opacity, _features_dc [P,1,3] and _features_rest [P,15,3]
  * and every render call first materialises exp / F.normalize / sigmoid / torch.cat of them
