@@ -118,6 +118,32 @@ __global__ void __launch_bounds__(ROW_BLOCK) move_rows_kernel(int P, const uint8
     }
 }
 
+// densify_and_split's tensor work (scene/gaussian_model_ht.py:630-654): the selected rows are replaced by N new
+// rows each, appended after the survivors:  dst = cat(src[~mask], repeat(src[mask], N))  -- what
+// densification_postfix followed by prune_points(cat(mask, zeros)) leaves.  offsets[] is the scan of `mask`
+// (count = selected rows), so a surviving row r lands at r - offsets[r].  zero_new: the N*count new rows are zeros
+// (Adam moments); skip_new: they are left for the caller to fill (positions / scales, which are computed).
+__global__ void __launch_bounds__(ROW_BLOCK) split_rows_kernel(int P, int N, uint32_t count, const uint8_t* __restrict__ mask,
+                                                               const uint32_t* __restrict__ offsets,
+                                                               const __grid_constant__ RowLaunch L) {
+    const htgs_row_tensor T = L.t[blockIdx.y];
+    const uint32_t* __restrict__ src = reinterpret_cast<const uint32_t*>(T.src);
+    uint32_t* __restrict__ dst = reinterpret_cast<uint32_t*>(T.dst);
+    const long long w = T.row_words, total = (long long)P * w;
+    const long long K = (long long)P - count;  // survivors
+    for (long long e = (long long)blockIdx.x * ROW_BLOCK + threadIdx.x; e < total; e += (long long)gridDim.x * ROW_BLOCK) {
+        const long long r = total < (1ll << 31) ? (long long)((uint32_t)e / (uint32_t)w) : e / w;
+        const long long c = e - r * w;
+        const uint32_t v = src[e];
+        const uint32_t o = offsets[r];
+        if (!mask[r]) {
+            dst[(r - o) * w + c] = v;
+        } else if (T.zero_new != 2) {
+            for (int n = 0; n < N; n++) dst[(K + (long long)n * count + o) * w + c] = T.zero_new ? 0u : v;
+        }
+    }
+}
+
 static int check_tensors(const char* who, int n, const htgs_row_tensor* t) {
     if (n < 0 || n > HTGS_ROWS_MAX_TENSORS || (n > 0 && !t)) { set_error("%s: need 0..%d tensors", who, HTGS_ROWS_MAX_TENSORS); return 1; }
     for (int k = 0; k < n; k++)
@@ -184,4 +210,30 @@ extern "C" int htgs_rows_compact(int P, const uint8_t* mask, const void* scratch
 extern "C" int htgs_rows_append(int P, const uint8_t* mask, const void* scratch, int n_tensors, const htgs_row_tensor* tensors,
                                 void* stream) {
     return move_rows<true>("htgs_rows_append", P, mask, scratch, n_tensors, tensors, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int htgs_rows_split(int P, int N, uint32_t count, const uint8_t* mask, const void* scratch, int n_tensors,
+                               const htgs_row_tensor* tensors, void* stream) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const char* who = "htgs_rows_split";
+    if (P <= 0 || n_tensors == 0) return 0;
+    if (N < 1) { set_error("%s: N must be >= 1", who); return 1; }
+    if (count > (uint32_t)P) { set_error("%s: count exceeds P", who); return 1; }
+    if (!mask || !scratch) { set_error("%s: null pointer", who); return 1; }
+    if (check_tensors(who, n_tensors, tensors)) return 1;
+    RowLaunch L;
+    L.n = n_tensors;
+    long long max_words = 0;
+    for (int k = 0; k < n_tensors; k++) {
+        L.t[k] = tensors[k];
+        const long long wds = (long long)P * tensors[k].row_words;
+        if (wds > max_words) max_words = wds;
+    }
+    const int nb = (P + ROW_BLOCK - 1) / ROW_BLOCK;
+    const uint32_t* offsets = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(scratch) + align_up((size_t)(nb + 1) * 4, 256));
+    const long long want = (max_words + ROW_BLOCK - 1) / ROW_BLOCK;
+    const dim3 grid((unsigned)(want < 148 * 16 ? (want < 1 ? 1 : want) : 148 * 16), (unsigned)n_tensors);
+    split_rows_kernel<<<grid, ROW_BLOCK, 0, st>>>(P, N, count, mask, offsets, L);
+    HTGS_LAUNCH_CHECK("split_rows_kernel");
+    return 0;
 }

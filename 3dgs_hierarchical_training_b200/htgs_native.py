@@ -65,6 +65,7 @@ _SIGNATURES = {
     "htgs_row_scan": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_rows_compact": (c_int, [c_int, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),
     "htgs_rows_append": (c_int, [c_int, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),
+    "htgs_rows_split": (c_int, [c_int, c_int, ctypes.c_uint32, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),
     "htgs_sort_scratch_bytes": (c_size_t, [c_int64]),
     "htgs_sort_pairs": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_sort_pairs_static": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -203,3 +203,73 @@ def clone_selected_to_optimizer(optimizer, selected_mask):
         g["params"][0] = newp
         new_params[g.get("name", str(gi))] = newp
     return new_params
+
+
+def split_selected_in_optimizer(optimizer, selected_mask, N, computed):
+    """densify_and_split's tensor work (scene/gaussian_model_ht.py:630-654): what `densification_postfix(new_*)`
+    followed by `prune_points(cat(selected, zeros(N * count)))` leaves -- every parameter becomes
+    cat(param[~selected], new rows) with new rows = the selected rows repeated N times, except for the groups named in
+    `computed` ({group name: [N * count, ...] tensor}; the reference computes new positions and scales, :633-643),
+    and both Adam moments become cat(moment[~selected], zeros).  One mask scan, one host read, one launch.
+    Returns {group name: new nn.Parameter}."""
+    if selected_mask.dtype not in (torch.bool, torch.uint8) or not selected_mask.is_cuda or selected_mask.dim() != 1:
+        raise RuntimeError("row mask must be a 1-D bool/uint8 CUDA tensor")
+    if N < 1:
+        raise RuntimeError("N must be >= 1")
+    mask = selected_mask.contiguous()
+    P, dev = int(mask.numel()), mask.device
+    groups = list(optimizer.param_groups)
+    lib = nat.lib()
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        scratch = torch.empty(lib.htgs_row_scan_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        pinned = torch.zeros(1, dtype=torch.int32).pin_memory()
+        nat.check(lib.htgs_row_scan(P, mask.data_ptr(), scratch.data_ptr(), pinned.data_ptr(), st), "htgs_row_scan")
+        torch.cuda.current_stream(dev).synchronize()
+        count = int(pinned[0]) & 0xFFFFFFFF
+        n_out = P - count + N * count
+        items = []  # (group index, what, src, dst, zero_new)
+        for gi, g in enumerate(groups):
+            if len(g["params"]) != 1:
+                raise RuntimeError("split_selected_in_optimizer expects one parameter per group")
+            p = g["params"][0]
+            if p.size(0) != P or p.element_size() != 4 or p.device != dev:
+                raise RuntimeError("parameter rows / dtype / device do not match the mask")
+            name = g.get("name", str(gi))
+            new_rows = computed.get(name)
+            if new_rows is not None and tuple(new_rows.shape) != (N * count,) + tuple(p.shape[1:]):
+                raise RuntimeError(f"computed[{name!r}] must have shape {(N * count,) + tuple(p.shape[1:])}, got {tuple(new_rows.shape)}")
+            src = p.data.contiguous()
+            items.append((gi, "param", src, torch.empty((n_out,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev),
+                          2 if new_rows is not None else 0))
+            stt = optimizer.state.get(p, None)
+            if stt is not None and "exp_avg" in stt:
+                for what in ("exp_avg", "exp_avg_sq"):
+                    items.append((gi, what, stt[what].contiguous(), torch.empty((n_out,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev), 1))
+        live = [it for it in items if it[2].numel() > 0]
+        for lo in range(0, len(live), nat.ROWS_MAX_TENSORS):
+            part = live[lo:lo + nat.ROWS_MAX_TENSORS]
+            arr = (nat.RowTensor * len(part))()
+            for j, (_, _, src, dst, z) in enumerate(part):
+                arr[j] = nat.RowTensor(src.data_ptr(), dst.data_ptr(), src.numel() // P, z)
+            if n_out > 0:
+                nat.check(lib.htgs_rows_split(P, int(N), count, mask.data_ptr(), scratch.data_ptr(), len(part), arr, st), "htgs_rows_split")
+        by_group = {}
+        for gi, what, _, dst, _ in items:
+            by_group.setdefault(gi, {})[what] = dst
+        new_params = {}
+        for gi, g in enumerate(groups):
+            name = g.get("name", str(gi))
+            if computed.get(name) is not None and count > 0:
+                by_group[gi]["param"][P - count:] = computed[name]
+            old = g["params"][0]
+            stored = optimizer.state.get(old, None)
+            newp = torch.nn.Parameter(by_group[gi]["param"].requires_grad_(True))
+            if stored is not None:
+                if "exp_avg" in by_group[gi]:
+                    stored["exp_avg"], stored["exp_avg_sq"] = by_group[gi]["exp_avg"], by_group[gi]["exp_avg_sq"]
+                del optimizer.state[old]
+                optimizer.state[newp] = stored
+            g["params"][0] = newp
+            new_params[name] = newp
+    return new_params

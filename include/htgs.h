@@ -231,18 +231,24 @@ int htgs_adam_step(int n_groups, const htgs_adam_group* groups, float beta1, flo
  *   htgs_rows_compact  dst[offsets[i]] = src[i] where mask[i] != 0          == torch src[mask]
  *   htgs_rows_append   dst[0:P] = src; dst[P + offsets[i]] = src[i] (or 0 when zero_new) where mask[i] != 0
  *                                                                            == torch.cat((src, src[mask])) / cat((src, zeros))
+ *   htgs_rows_split    dst = cat(src[mask == 0], repeat(src[mask != 0], N)): what densification_postfix followed by
+ *                      prune_points(cat(mask, zeros)) leaves in densify_and_split (:630-654).  count = the total
+ *                      htgs_row_scan reported.  zero_new = 1: the N*count new rows are zeros (Adam moments);
+ *                      zero_new = 2: they are not written (the caller fills computed positions / scales).
  * mask: uint8/bool [P]; every tensor is [P, row_words] 32-bit words, contiguous; dst sized by the caller. */
 #define HTGS_ROWS_MAX_TENSORS 24
 typedef struct {
     const void* src;
     void* dst;
     int row_words; /* 32-bit words per row */
-    int zero_new;  /* htgs_rows_append only: appended rows are zero (Adam moments of cloned Gaussians) */
+    int zero_new;  /* append / split: 1 = new rows are zero (Adam moments of new Gaussians); split only: 2 = new rows untouched */
 } htgs_row_tensor;
 size_t htgs_row_scan_scratch_bytes(int P);
 int htgs_row_scan(int P, const uint8_t* mask, void* scratch, uint32_t* count_pinned_host, void* stream);
 int htgs_rows_compact(int P, const uint8_t* mask, const void* scratch, int n_tensors, const htgs_row_tensor* tensors, void* stream);
 int htgs_rows_append(int P, const uint8_t* mask, const void* scratch, int n_tensors, const htgs_row_tensor* tensors, void* stream);
+int htgs_rows_split(int P, int N, uint32_t count, const uint8_t* mask, const void* scratch, int n_tensors,
+                    const htgs_row_tensor* tensors, void* stream);
 
 /* ---- un-activated, un-concatenated parameters (opt-in) ----
  * The HT model stores _scaling, _rotation, _opacity, _features_dc [P,1,3] and _features_rest [P,15,3]

@@ -113,6 +113,47 @@ def test_optimizer_surgery_matches_reference_and_training_continues(op):
         assert torch.equal(new_a[k], new_b[k]), k
 
 
+def _reference_split(opt, sel, N, new_xyz, new_scaling):
+    """densify_and_split (:630-654): densification_postfix(new rows) then prune_points(cat(sel, zeros))."""
+    new = {}
+    for group in opt.param_groups:
+        p = group["params"][0]
+        new[group["name"]] = {"xyz": new_xyz, "scaling": new_scaling}.get(group["name"])
+        if new[group["name"]] is None:
+            new[group["name"]] = p[sel].repeat(N, *([1] * (p.dim() - 1)))
+    for group in opt.param_groups:  # cat_tensors_to_optimizer
+        ext = new[group["name"]]
+        stored = opt.state.get(group["params"][0], None)
+        stored["exp_avg"] = torch.cat((stored["exp_avg"], torch.zeros_like(ext)), dim=0)
+        stored["exp_avg_sq"] = torch.cat((stored["exp_avg_sq"], torch.zeros_like(ext)), dim=0)
+        del opt.state[group["params"][0]]
+        group["params"][0] = torch.nn.Parameter(torch.cat((group["params"][0], ext), dim=0).requires_grad_(True))
+        opt.state[group["params"][0]] = stored
+    prune_filter = torch.cat((sel, torch.zeros(N * int(sel.sum()), device="cuda", dtype=bool)))
+    return _reference_prune(opt, ~prune_filter)
+
+
+@pytest.mark.parametrize("N,frac", [(2, 0.07), (3, 0.5), (2, 0.0), (2, 1.0)])
+def test_split_matches_postfix_then_prune(N, frac):
+    import htgs_optim
+    P = 10_007
+    sel = (torch.rand(P, generator=torch.Generator().manual_seed(N)) < frac).cuda()
+    count = int(sel.sum())
+    a = _make_optimizer(P, htgs_optim.FusedAdam)
+    b = _make_optimizer(P, htgs_optim.FusedAdam)
+    g = torch.Generator().manual_seed(99)
+    new_xyz, new_scaling = torch.randn(N * count, 3, generator=g).cuda(), torch.randn(N * count, 3, generator=g).cuda()
+    new_a = htgs_optim.split_selected_in_optimizer(a, sel, N, {"xyz": new_xyz, "scaling": new_scaling})
+    new_b = _reference_split(b, sel, N, new_xyz, new_scaling)
+    for k in new_b:
+        assert new_a[k].shape[0] == P - count + N * count
+        assert torch.equal(new_a[k], new_b[k]), k
+        sa, sb = a.state[new_a[k]], b.state[new_b[k]]
+        assert torch.equal(sa["exp_avg"], sb["exp_avg"]) and torch.equal(sa["exp_avg_sq"], sb["exp_avg_sq"]), k
+    with pytest.raises(RuntimeError):
+        htgs_optim.split_selected_in_optimizer(a, sel[:-1], N, {})
+
+
 def test_row_ops_reject_bad_arguments():
     import htgs_optim
     t = torch.zeros(10, 3).cuda()
