@@ -49,26 +49,35 @@ struct Reduce10 {
     __device__ __forceinline__ float run(const float (&v)[BWD_NV]) const {
         const unsigned full = 0xffffffffu;
         float a[5], c[3], d[2];
+        float ak[5], ar[5];
 #pragma unroll
         for (int k = 0; k < 5; k++) {
             const float send = b4 ? v[k] : v[5 + k];
-            const float keep = b4 ? v[5 + k] : v[k];
-            a[k] = keep + __shfl_xor_sync(full, send, 16);
+            ak[k] = b4 ? v[5 + k] : v[k];
+            ar[k] = __shfl_xor_sync(full, send, 16);
         }
+        up2(add2(pk2(ak[0], ak[1]), pk2(ar[0], ar[1])), a[0], a[1]);  // packed adds: one issue slot per pair
+        up2(add2(pk2(ak[2], ak[3]), pk2(ar[2], ar[3])), a[2], a[3]);
+        a[4] = ak[4] + ar[4];
+        float ck[3], cr[3];
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             const float hi = (3 + k < 5) ? a[(3 + k < 5) ? 3 + k : 0] : 0.f;
             const float send = b3 ? a[k] : hi;
-            const float keep = b3 ? hi : a[k];
-            c[k] = keep + __shfl_xor_sync(full, send, 8);
+            ck[k] = b3 ? hi : a[k];
+            cr[k] = __shfl_xor_sync(full, send, 8);
         }
+        up2(add2(pk2(ck[0], ck[1]), pk2(cr[0], cr[1])), c[0], c[1]);
+        c[2] = ck[2] + cr[2];
+        float dk[2], dr[2];
 #pragma unroll
         for (int k = 0; k < 2; k++) {
             const float hi = (k == 0) ? c[2] : 0.f;
             const float send = b2 ? c[k] : hi;
-            const float keep = b2 ? hi : c[k];
-            d[k] = keep + __shfl_xor_sync(full, send, 4);
+            dk[k] = b2 ? hi : c[k];
+            dr[k] = __shfl_xor_sync(full, send, 4);
         }
+        up2(add2(pk2(dk[0], dk[1]), pk2(dr[0], dr[1])), d[0], d[1]);
         const float send = b1 ? d[0] : d[1];
         const float keep = b1 ? d[1] : d[0];
         float e = keep + __shfl_xor_sync(full, send, 2);
@@ -131,6 +140,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 #pragma unroll
     for (int w = 0; w < BLEND_WARPS; w++) block_last = max(block_last, s_warp_last[w]);
 
+    const uint64_t pxy = pk2(pxf, pyf), dd_d0 = pk2(dd, d0), d1_d2 = pk2(d1, d2);
     Reduce10 red;
     red.init(lane);
     const uint32_t sg_base = smem_u32(s_g);
@@ -162,10 +172,14 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
                 const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
-                const float4 q0 = lds128(a);       // mean.xy, conic.xy
-                const float4 q1 = lds128(a + 16);  // conic.z, opacity, r, g
-                const float dx = SB(q0.x, pxf), dy = SB(q0.y, pyf);
-                const float power = pair_power(dx, dy, q0.z, q0.w, q1.x);
+                const float4 q0 = lds128(a);       // mean.xy, conic.x, conic.z
+                const float4 q1 = lds128(a + 16);  // conic.y, opacity, r, g
+                const uint64_t dxy = sub2(pk2(q0.x, q0.y), pxy);   // (dx, dy)
+                float dx, dy, tx, ty, my, mc;
+                up2(dxy, dx, dy);
+                up2(mul2(dxy, pk2(q0.z, q0.w)), tx, ty);                  // (dx*cx, dy*cz)
+                up2(mul2(pk2(dy, dy), pk2(ty, MU(dx, q1.x))), my, mc);    // (dy*(dy*cz), dy*(dx*cy))
+                const float power = FM(FM(dx, tx, my), -0.5f, -mc);       // pair_power()
                 const float G = expf(power);
                 const float alpha = fminf(0.99f, MU(q1.y, G));
                 // `contributor` after its decrement is chunk_top - b (backward.cu:517-519)
@@ -183,24 +197,24 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     rinv = fmaf(fmaf(-one_m_a, rinv, 1.f), rinv, rinv);
                     T = T * rinv;
                     const float aT = alpha * T;
-                    const float Cd = fmaf(q2.y, dd, fmaf(q2.x, d2, fmaf(q1.w, d1, fmaf(q1.z, d0, da))));
+                    const float Cd = fmaf(q2.y, dd, fmaf(q2.x, d2, fmaf(q1.w, d1, fmaf(q1.z, d0, da))));  // q1.zw = r, g
                     A = fmaf(last_alpha, Cprev, (1.f - last_alpha) * A);
                     Cprev = Cd;
                     last_alpha = alpha;
                     float dL_dopa = (Cd - A) * T;
                     if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
                     const float w = G * dL_dopa;
-                    const float wdx = w * dx, wdy = w * dy;
+                    const uint64_t wd = mul2(pk2(w, w), dxy);  // (w*dx, w*dy)
+                    float wdx, wdy;
+                    up2(wd, wdx, wdy);
                     v[0] = w;          // -> dL/dopacity, and scaled by opacity the common factor below
                     v[1] = wdx;        // first moments  -> dL/dmean2D
                     v[2] = wdy;
-                    v[3] = aT * dd;    // dL/ddepth
-                    v[4] = wdx * dx;   // second moments -> dL/dconic
+                    up2(mul2(wd, dxy), v[4], v[6]);  // second moments w*dx*dx, w*dy*dy -> dL/dconic
                     v[5] = wdx * dy;
-                    v[6] = wdy * dy;
-                    v[7] = aT * d0;    // dL/dcolour
-                    v[8] = aT * d1;
-                    v[9] = aT * d2;
+                    const uint64_t aTaT = pk2(aT, aT);
+                    up2(mul2(aTaT, dd_d0), v[3], v[7]);  // dL/ddepth, dL/dcolour r
+                    up2(mul2(aTaT, d1_d2), v[8], v[9]);  // dL/dcolour g, b
                 }
                 float total = 0.f;
                 if (__any_sync(0xffffffffu, live)) total = red.run(v);
@@ -225,7 +239,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             // moments -> gradients (backward.cu:582-598), per-Gaussian constants applied once here
             const float4 q0 = s_g[tid].q0;
             const float4 q1 = s_g[tid].q1;
-            const float cx = q0.z, cy = q0.w, cz = q1.x, op = q1.y;
+            const float cx = q0.z, cz = q0.w, cy = q1.x, op = q1.y;
             const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:490-491
             const float gmx = -op * (cx * s[1] + cy * s[2]) * ddelx_dx;
             const float gmy = -op * (cz * s[2] + cy * s[1]) * ddely_dy;

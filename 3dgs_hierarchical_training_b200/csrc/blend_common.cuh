@@ -27,7 +27,8 @@ __device__ __forceinline__ int warp_block_x(int w) { return (w & 1) * 8; }
 __device__ __forceinline__ int warp_block_y(int w) { return (w >> 1) * 4; }
 
 // One staged Gaussian in shared memory (48 B, 16-byte aligned):
-//   q0 = (mean.x, mean.y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, depth, -, -)
+//   q0 = (mean.x, mean.y, conic.x, conic.z)   q1 = (conic.y, opacity, r, g)   q2 = (b, depth, -, -)
+// conic.x and conic.z sit next to each other so that (dx*cx, dy*cz) is one packed multiply (below).
 struct __align__(16) StagedGaussian {
     float4 q0, q1, q2;
 };
@@ -44,9 +45,20 @@ __device__ __forceinline__ float2 lds64(uint32_t a) {
     asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a) : "memory");
     return v;
 }
+// Packed FP32 pairs (sm_100 FADD2 / FMUL2 / FFMA2): one issue slot for two IEEE-rounded operations, bit-identical to
+// the scalar ones.  The blend loops are issue-bound, so every pair formed is an instruction saved.  Only products
+// that are NOT followed by a packed add are written as mul2: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2
+// even with explicit rounding modifiers, which would change results.
+__device__ __forceinline__ uint64_t pk2(float a, float b) { uint64_t r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void up2(uint64_t r, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) { uint64_t d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) { uint64_t d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) { uint64_t d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) { uint64_t d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
 __device__ __forceinline__ void stage_gaussian(StagedGaussian* dst, float2 xy, float4 co, float4 f) {
-    dst->q0 = make_float4(xy.x, xy.y, co.x, co.y);
-    dst->q1 = make_float4(co.z, co.w, f.x, f.y);
+    dst->q0 = make_float4(xy.x, xy.y, co.x, co.z);
+    dst->q1 = make_float4(co.y, co.w, f.x, f.y);
     dst->q2 = make_float4(f.z, f.w, 0.f, 0.f);
 }
 

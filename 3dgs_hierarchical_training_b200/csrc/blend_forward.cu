@@ -41,7 +41,9 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     const int n = (int)(range.y - range.x);
     const uint32_t sg_base = smem_u32(s_g);
 
-    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, dsum = 0.f;
+    float T = 1.0f, wsum = 0.f;
+    uint64_t C01 = pk2(0.f, 0.f), C2d = pk2(0.f, 0.f);  // (C0, C1) and (C2, depth sum) as packed pairs
+    const uint64_t pxy = pk2(pxf, pyf);
     uint32_t last_contributor = 0;
     uint32_t st_blended = 0, st_tested = 0, st_done_pos = 0;
     uint32_t st_hist[7] = {0, 0, 0, 0, 0, 0, 0};  // warp visits by number of blending lanes: 0, 1, 2-4, 5-8, 9-16, 17-24, 25-32
@@ -69,10 +71,17 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
                 const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
-                const float4 q0 = lds128(a);       // mean.xy, conic.xy
-                const float4 q1 = lds128(a + 16);  // conic.z, opacity, r, g
-                const float dx = SB(q0.x, pxf), dy = SB(q0.y, pyf);
-                const float power = pair_power(dx, dy, q0.z, q0.w, q1.x);
+                const float4 q0 = lds128(a);       // mean.xy, conic.x, conic.z
+                const float4 q1 = lds128(a + 16);  // conic.y, opacity, r, g
+                const uint64_t d2 = sub2(pk2(q0.x, q0.y), pxy);     // (dx, dy)
+                const uint64_t t2 = mul2(d2, pk2(q0.z, q0.w));      // (dx*cx, dy*cz)
+                float dx, dy, tx, ty;
+                up2(d2, dx, dy);
+                up2(t2, tx, ty);
+                // pair_power(): fma(fma(dx, dx*cx, dy*(dy*cz)), -0.5, -(dy*(dx*cy)))
+                float my, mc;
+                up2(mul2(pk2(dy, dy), pk2(ty, MU(dx, q1.x))), my, mc);  // (dy*(dy*cz), dy*(dx*cy))
+                const float power = FM(FM(dx, tx, my), -0.5f, -mc);
                 const float alpha = fminf(0.99f, MU(q1.y, expf(power)));
                 const float test_T = MU(T, SB(1.0f, alpha));
                 // the reference's three rejections (forward.cu:340-355) as one predicate chain
@@ -91,11 +100,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 }
                 if (live && !kill) {
                     const float2 q2 = lds64(a + 32);  // b, depth
-                    C0 = FM(T, MU(alpha, q1.z), C0);
-                    C1 = FM(T, MU(alpha, q1.w), C1);
-                    C2 = FM(T, MU(alpha, q2.x), C2);
+                    const uint64_t aa = pk2(alpha, alpha), TT = pk2(T, T);
+                    C01 = fma2(TT, mul2(aa, pk2(q1.z, q1.w)), C01);  // C += T * (alpha * c), forward.cu:359-361
+                    C2d = fma2(TT, mul2(aa, pk2(q2.x, q2.y)), C2d);
                     wsum = FM(T, alpha, wsum);
-                    dsum = FM(T, MU(alpha, q2.y), dsum);
                     T = test_T;
                     last_contributor = chunk_pos + (uint32_t)b;
                     if (STATS) st_blended++;
@@ -116,6 +124,9 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         }
         return;
     }
+    float C0, C1, C2, dsum;
+    up2(C01, C0, C1);
+    up2(C2d, C2, dsum);
     if (inside) {
         const size_t pix = (size_t)py * W + px;
         const size_t plane = (size_t)H * W;
