@@ -263,7 +263,7 @@ def run_ours(args, rank, world, local_rank):
             for k, v in host_cam.items():
                 cam[k] = v.to(dev, non_blocking=True)
             color, radii = step(cam, upg, before_backward=lambda: main.wait_event(copied))
-            s = (color.detach().double().sum() + params["opacities"].grad.double().sum()).reshape(1)
+            s = (color.detach().sum(dtype=torch.float64) + params["opacities"].grad.sum(dtype=torch.float64)).reshape(1)
             result.copy_(s, non_blocking=False)  # device->host read of the step's scalar result
             return float(result[0].detach())
 
