@@ -32,7 +32,7 @@
 
 namespace htgs {
 
-constexpr int BWD_BATCH = 128;
+constexpr int BWD_BATCH = 128;  // 96 / 112 / 64 per batch and 5-6 CTAs per SM (48 / 40 registers) all measured slower
 constexpr int BWD_NV = 10;
 
 // value order inside the kernel: 0 w 1 w*dx 2 w*dy 3 depth-grad 4..6 w*dx*dx, w*dx*dy, w*dy*dy 7..9 rgb-grad

@@ -19,8 +19,10 @@ constexpr int FWD_BATCH = 256;
 // pair tests the reference's one-thread-per-pixel loop would execute (list entries walked
 // until the pixel saturates), to stats[1] the blended pairs, to stats[2] the pair tests this
 // kernel executes after reach-mask culling.
+// 6 CTAs per SM (40 registers, no spills): 0.514 ms against 0.538 ms at 4 CTAs and 0.525 ms at 8 (config 3)
+constexpr int FWD_MIN_BLOCKS = 6;
 template <bool STATS>
-__global__ void __launch_bounds__(HTGS_TILE_PIX)
+__global__ void __launch_bounds__(HTGS_TILE_PIX, FWD_MIN_BLOCKS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                      const float4* __restrict__ feat, const float* __restrict__ bg, float* __restrict__ out_color,
