@@ -94,8 +94,10 @@ __device__ __forceinline__ void load_sh_and_eval(const float* __restrict__ shp, 
 
 // RAW = true: `scales`, `rotations`, `opacities` are the un-activated parameters, `shs` is _features_dc
 // [P,1,3] and `shs_rest` is _features_rest [P,15,3] (raw_params.cuh); M is 16.
+// 4 CTAs per SM (64 registers, no spills): 0.065 ms against 0.070 ms at the compiler's own 70 registers / 3 CTAs
+constexpr int PRE_MB = 4;
 template <bool RAW>
-__global__ void __launch_bounds__(HTGS_PRE_BLOCK)
+__global__ void __launch_bounds__(HTGS_PRE_BLOCK, PRE_MB)
 preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
                   float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
                   const float* __restrict__ shs, const float* __restrict__ shs_rest,
