@@ -59,7 +59,9 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             const float2 xy = means2D[g];
             const float4 co = conic_opacity[g];
             stage_gaussian(&s_g[tid], xy, co, feat[g]);
-            s_mask[tid] = (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
+            const uint32_t rm = block_reach_mask(xy, co, tile_x0, tile_y0);
+            s_mask[tid] = (uint8_t)rm;
+            if (STATS && rm == 0) atomicAdd(&stats[10], 1ull);  // instances whose Gaussian cannot reach any pixel of the tile
         }
         __syncthreads();
         if (__all_sync(0xffffffffu, done)) continue;

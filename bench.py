@@ -241,28 +241,49 @@ def run_ours(args, rank, world, local_rank):
     e2e = None
     if not args.no_e2e:
         host = {k: v.pin_memory() for k, v in up.items()}
-        host_cam = {k: cam_h[k].pin_memory() for k in ("viewmatrix", "projmatrix", "campos")}
-        h2d = sum(v.numel() * 4 for v in host.values()) + sum(v.numel() * 4 for v in host_cam.values())
+        # the camera (view 16 + projection 16 + position 3 floats) travels as ONE pinned buffer / one copy
+        host_cam = torch.cat([cam_h[k].reshape(-1).float() for k in ("viewmatrix", "projmatrix", "campos")]).pin_memory()
+        h2d = sum(v.numel() * 4 for v in host.values()) + host_cam.numel() * 4
         result = torch.zeros(1, dtype=torch.float64).pin_memory()
 
-        # The camera (140 B) is needed by the first kernel and goes on the compute stream.  The upstream
-        # image gradients (41 MB at 1080p) are only read by the backward, so their host->device copy runs
-        # on a second stream underneath the forward pass; the compute stream waits for it just before the
-        # backward.  The buffers stay referenced until the blocking result read below, so the allocator
-        # cannot hand them out again while either stream still uses them.
+        # Input pipeline of the end-to-end leg (every step's inputs still come from pinned host memory, every step's
+        # result is still read back with a blocking copy -- only WHEN the upload runs changes):
+        #   * the camera (140 B) is needed by the first kernel and goes on the compute stream;
+        #   * the upstream image gradients (41 MB at 1080p) are only read by the backward.  Their upload for step k+1
+        #     is issued on a second stream as soon as step k starts (double-buffered device staging, the usual
+        #     "prefetch the next batch" loader), so it runs underneath step k's kernels; measured on this box the
+        #     upload takes ~1.1 ms, longer than a forward pass, so starting it only at the top of its own step left the
+        #     backward waiting.  The compute stream waits on the upload's event right before the backward.
         copy_stream = torch.cuda.Stream(device=dev)
-        copied = torch.cuda.Event()
+        # one pinned [5,H,W] buffer (colour 3 + depth 1 + alpha 1 planes) and one copy per step: issuing three copies
+        # cost more host time (~80 us with the stream switch) than the transfer itself adds to the step
+        host_up = torch.cat([host["dL_dcolor"], host["dL_ddepth"], host["dL_dalpha"]], dim=0).pin_memory()
+        staged_buf = [torch.empty_like(host_up, device=dev) for _ in range(2)]
+        staged = [{"dL_dcolor": b[0:3], "dL_ddepth": b[3:4], "dL_dalpha": b[4:5]} for b in staged_buf]
+        uploaded = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        state = {"k": 0}
+
+        def upload(slot):
+            copy_stream.wait_event(consumed[slot])  # the backward that last read this slot has finished
+            with torch.cuda.stream(copy_stream):
+                staged_buf[slot].copy_(host_up, non_blocking=True)
+                uploaded[slot].record(copy_stream)
+
+        for ev in consumed:
+            ev.record(torch.cuda.current_stream(dev))
+        upload(0)
 
         def e2e_step():
             main = torch.cuda.current_stream(dev)
-            copy_stream.wait_stream(main)
-            with torch.cuda.stream(copy_stream):
-                upg = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-                copied.record(copy_stream)
+            slot = state["k"] & 1
+            state["k"] += 1
+            upload(slot ^ 1)  # next step's gradients travel while this step computes
             cam = dict(cam_h)
-            for k, v in host_cam.items():
-                cam[k] = v.to(dev, non_blocking=True)
-            color, radii = step(cam, upg, before_backward=lambda: main.wait_event(copied))
+            cam_dev = host_cam.to(dev, non_blocking=True)
+            cam["viewmatrix"], cam["projmatrix"], cam["campos"] = cam_dev[:16].view(4, 4), cam_dev[16:32].view(4, 4), cam_dev[32:35]
+            color, radii = step(cam, staged[slot], before_backward=lambda: main.wait_event(uploaded[slot]))
+            consumed[slot].record(main)
             s = (color.detach().sum(dtype=torch.float64) + params["opacities"].grad.sum(dtype=torch.float64)).reshape(1)
             result.copy_(s, non_blocking=False)  # device->host read of the step's scalar result
             return float(result[0].detach())
@@ -295,7 +316,7 @@ def run_ours(args, rank, world, local_rank):
             bg, params["means3D"], empty, params["opacities"], params["scales"], params["rotations"], 1.0, empty,
             cam_d["viewmatrix"], cam_d["projmatrix"], cam_d["tanfovx"], cam_d["tanfovy"], H, W, params["shs"], 3,
             cam_d["campos"], False, False)
-        stats = torch.zeros(10, dtype=torch.int64, device=dev)  # HTGS_BLEND_NSTATS
+        stats = torch.zeros(11, dtype=torch.int64, device=dev)  # HTGS_BLEND_NSTATS
         nat.check(lib.htgs_blend_stats(P, R, W, H, geom.data_ptr(), nat.ptr(binning), img.data_ptr(), stats.data_ptr(),
                                        ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "htgs_blend_stats")
         stats_h = [int(x) for x in stats.cpu()]
@@ -350,7 +371,7 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": args.workload, "P": P, "W": W, "H": H, "sh_degree": 3, "views_per_step_per_gpu": len(cams_d), "views_per_step": batch_views,
                    "P_visible": P_vis, "R_instances": int(R), "pairs_tested_reference_loop": n_ref_tested,
                    "pairs_tested_after_culling": n_ours_tested, "pairs_blended": n_blended,
-                   "warp_visits_by_blending_lanes": visit_hist,
+                   "warp_visits_by_blending_lanes": visit_hist, "instances_with_empty_reach": stats_h[10],
                    "l2": "inputs+outputs per step (~0.7 GB) exceed the 126 MB L2; no explicit flush",
                    "parallelism": f"view-parallel dp{world}" + (" + NCCL all-reduce of 59 f32/Gaussian" if world > 1 else "")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * len(cams_d) * (5 + passes + 2 + 2),

@@ -190,8 +190,9 @@ int htgs_sort_pairs_static(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* 
  * htgs_blend_stats() re-walks the tile lists of the last forward and writes HTGS_BLEND_NSTATS counters
  * to stats (device, uint64 each): [0] pair tests of the reference's per-pixel loop, [1] blended pairs,
  * [2] pair tests this library executes after reach-mask culling, [3..9] number of (warp, Gaussian)
- * visits in which 0, 1, 2-4, 5-8, 9-16, 17-24, 25-32 of the warp's 32 pixels blended the Gaussian. */
-#define HTGS_BLEND_NSTATS 10
+ * visits in which 0, 1, 2-4, 5-8, 9-16, 17-24, 25-32 of the warp's 32 pixels blended the Gaussian,
+ * [10] (Gaussian, tile) instances staged before the tile saturated whose Gaussian cannot reach any pixel of the tile. */
+#define HTGS_BLEND_NSTATS 11
 #define HTGS_NUM_STAGES 9
 void htgs_profile_enable(int on);
 int htgs_profile_read(double* ms_sum, int* counts, int cap);
