@@ -394,6 +394,14 @@ def cpu_baseline(workload, steps=1, warm=False):
     sc = {k: v.numpy() for k, v in scene.items()}
     upn = {k: v.numpy() for k, v in up.items()}
 
+    # all the host threads this process may use, whatever OMP_NUM_THREADS says: torchrun exports OMP_NUM_THREADS=1 to
+    # its workers, which would time the CPU baseline on a single core
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    golden.set_num_threads(max(1, avail))
+
     def one():
         st = golden.forward(sc["means3D"], sc["opacities"], cam, bg, 3, shs=sc["shs"], scales=sc["scales"], rotations=sc["rotations"])
         golden.backward(st, upn["dL_dcolor"], upn["dL_ddepth"], upn["dL_dalpha"])
