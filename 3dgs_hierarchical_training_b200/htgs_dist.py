@@ -25,9 +25,35 @@ class FlatGradReducer:
     """Packs the five parameter gradients into one contiguous buffer, all-reduces it once (sum),
     and hands the reduced views back -- one collective of 236 B/Gaussian instead of five."""
 
-    def __init__(self, P, device, dtype=torch.float32):
+    def __init__(self, P, device, dtype=torch.float32, peer_memory=False):
+        """peer_memory=True: the flat buffer lives in torch symmetric memory (mapped by every rank of the default
+        process group) and `all_reduce` runs this library's own two-shot kernel over NVLink peer loads/stores
+        (htgs_allreduce_p2p) between two cross-GPU barriers instead of calling NCCL.  CUDA + initialised process group
+        required; construction raises if the peers cannot map each other's memory."""
         self.P = P
-        self.flat = torch.zeros(P * FLOATS_PER_GAUSSIAN, device=device, dtype=dtype)
+        n = P * FLOATS_PER_GAUSSIAN
+        self._peer = None
+        self.collective = "nccl"
+        if peer_memory:
+            import ctypes
+            import torch.distributed._symmetric_memory as symm_mem
+            if dtype != torch.float32:
+                raise RuntimeError("peer-memory all-reduce is float32 only")
+            n_pad = (n + 3) // 4 * 4  # the kernel moves 128-bit words
+            buf = symm_mem.empty(n_pad, dtype=torch.float32, device=device)
+            hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
+            buf.zero_()
+            off = buf.data_ptr() - int(hdl.buffer_ptrs[hdl.rank])
+            table = (ctypes.c_void_p * hdl.world_size)(*[int(p) + off for p in hdl.buffer_ptrs])
+            mc = int(hdl.multicast_ptr) if getattr(hdl, "has_multicast_support", lambda *a: False) and hdl.multicast_ptr else 0
+            self._peer = dict(buf=buf, hdl=hdl, table=table, n_pad=n_pad, mc=(mc + off) if mc else 0)
+            # peer loads move 2(N-1)/N buffers per link direction, the switch multicast about one: NVLS from 3 ranks up
+            self.collective = "multimem" if (mc and hdl.world_size > 2 and peer_memory != "p2p") or peer_memory == "multimem" else "p2p"
+            if self.collective == "multimem" and not mc:
+                raise RuntimeError("multimem all-reduce requested but the symmetric-memory handle has no multicast address")
+            self.flat = buf[:n]
+        else:
+            self.flat = torch.zeros(n, device=device, dtype=dtype)
         self.slices = {}
         o = 0
         for name, per in zip(PARAM_ORDER, (3, 48, 1, 3, 4)):
@@ -71,6 +97,24 @@ class FlatGradReducer:
         return self.flat
 
     def all_reduce(self, average=False):
+        if self._peer is not None:
+            import ctypes
+            import htgs_native as nat
+            pm = self._peer
+            dev = self.flat.device
+            with torch.cuda.device(dev):
+                st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+                pm["hdl"].barrier(channel=0)  # every rank's gradients are complete (stream-ordered, device-side)
+                if self.collective == "multimem":
+                    nat.check(nat.lib().htgs_allreduce_multimem(ctypes.c_void_p(pm["mc"]), pm["hdl"].rank, pm["hdl"].world_size,
+                                                                pm["n_pad"], st), "htgs_allreduce_multimem")
+                else:
+                    nat.check(nat.lib().htgs_allreduce_p2p(pm["table"], pm["hdl"].rank, pm["hdl"].world_size, pm["n_pad"], st),
+                              "htgs_allreduce_p2p")
+                pm["hdl"].barrier(channel=0)  # every rank's slice has been written everywhere
+            if average:
+                self.flat.div_(dist.get_world_size())
+            return self.flat
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
             if average:

@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--workload", default="config3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--collective", default="auto", choices=["auto", "nccl", "p2p", "multimem"],
+                    help="gradient all-reduce for --gpus > 1: own peer-memory kernels (auto picks p2p at 2 ranks, multimem above) or NCCL")
     return ap.parse_args()
 
 
@@ -170,7 +172,19 @@ def run_ours(args, rank, world, local_rank):
     cams_d = [{k: (v.to(dev) if hasattr(v, "to") else v) for k, v in c.items()} for c in cams_h]
     cam_d = cams_d[0]
     import htgs_dist
-    reducer = htgs_dist.FlatGradReducer(P, dev) if world > 1 else None
+    reducer = None
+    if world > 1:
+        # gradient all-reduce: this library's own kernel over NVLink peer memory / NVSwitch multicast when the ranks
+        # can map each other's buffers (torch symmetric memory), NCCL otherwise or with --collective nccl
+        if args.collective != "nccl":
+            try:
+                reducer = htgs_dist.FlatGradReducer(P, dev, peer_memory=True if args.collective == "auto" else args.collective)
+            except Exception as e:  # noqa: BLE001 - any failure to set up peer mappings means NCCL
+                if args.collective != "auto":
+                    raise
+                print(f"[bench] peer-memory all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+        if reducer is None:
+            reducer = htgs_dist.FlatGradReducer(P, dev)
     if reducer is not None and len(cams_d) == 1:
         reducer.install_arena()  # one backward per parameter per step: gradients land in the all-reduce buffer
 
@@ -373,7 +387,7 @@ def run_ours(args, rank, world, local_rank):
                    "pairs_tested_after_culling": n_ours_tested, "pairs_blended": n_blended,
                    "warp_visits_by_blending_lanes": visit_hist, "instances_with_empty_reach": stats_h[10],
                    "l2": "inputs+outputs per step (~0.7 GB) exceed the 126 MB L2; no explicit flush",
-                   "parallelism": f"view-parallel dp{world}" + (" + NCCL all-reduce of 59 f32/Gaussian" if world > 1 else "")},
+                   "parallelism": f"view-parallel dp{world}" + (f" + all-reduce of 59 f32/Gaussian ({reducer.collective})" if world > 1 else "")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * len(cams_d) * (5 + passes + 2 + 2),
         "roofline": roofline, "roofline_hbm": roofline_hbm, "roofline_stages": stage_report, "impl": "ours",
     }

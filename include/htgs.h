@@ -221,6 +221,21 @@ int htgs_densification_stats(int P, const int* radii, const float* grad_means2D,
 int htgs_adam_step(int n_groups, const htgs_adam_group* groups, float beta1, float beta2, float eps,
                    long long step, void* stream);
 
+/* ---- gradient all-reduce over NVLink peer memory (opt-in, no reference counterpart) ----
+ * peer_buffers: HOST array of `world` device pointers to the same-sized float32 buffer on every rank, entry `rank`
+ * being the caller's own (all mapped into the caller's address space, e.g. by torch symmetric memory or cudaIpc).
+ * Two-shot: this rank sums slice `rank` of all buffers in the fixed order 0..world-1 and writes the result into that
+ * slice of EVERY buffer; run on all ranks it leaves the element-wise sum everywhere, bit-identical on all ranks.
+ * The caller provides the cross-GPU ordering: every rank's buffer must be complete before any rank's kernel starts,
+ * and every rank's kernel must have finished before any rank reads the result (a barrier before and after).
+ * numel must be a multiple of 4; world <= 8. */
+int htgs_allreduce_p2p(const void* const* peer_buffers, int rank, int world, long long numel, void* stream);
+/* Same contract, but through one NVSwitch MULTICAST address that maps the buffer of every rank (cuMulticast* /
+ * torch symmetric memory `multicast_ptr`): the switch sums the ranks' elements on the load (multimem.ld_reduce) and
+ * replicates the store (multimem.st), so each GPU moves about one buffer per direction at any world size.  The
+ * summation order inside the switch is the hardware's; all ranks still receive the same bits. */
+int htgs_allreduce_multimem(void* multicast_buffer, int rank, int world, long long numel, void* stream);
+
 /* ---- row surgery for prune / clone (first half; opt-in) ----
  * Replaces the per-tensor boolean-mask indexing of _prune_optimizer / prune_points and the per-tensor
  * torch.cat of cat_tensors_to_optimizer / densification_postfix in the clone case
