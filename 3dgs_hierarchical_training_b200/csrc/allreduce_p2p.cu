@@ -9,6 +9,8 @@
 // 236 MB in 0.49 ms at 2 GPUs and 0.64 ms at 8, far from the 900 GB/s per direction the links offer.
 #include "../../include/htgs.h"
 #include "common.cuh"
+#include <algorithm>
+#include <cstdlib>
 
 namespace htgs {
 
@@ -39,8 +41,8 @@ allreduce_multimem_kernel(float4* __restrict__ mc, int rank, int world, long lon
     const long long per = (n4 + world - 1) / world;
     const long long lo = (long long)rank * per;
     const long long hi = lo + per < n4 ? lo + per : n4;
-    const long long stride = (long long)gridDim.x * AR_THREADS;
-    for (long long i0 = lo + (long long)blockIdx.x * AR_THREADS + threadIdx.x; i0 < hi; i0 += stride * AR_UNROLL) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * AR_UNROLL) {
         float4 acc[AR_UNROLL];
 #pragma unroll
         for (int u = 0; u < AR_UNROLL; u++) {
@@ -136,7 +138,15 @@ extern "C" int htgs_allreduce_multimem(void* multicast_buffer, int rank, int wor
     if (numel <= 0 || world == 1) return 0;
     if (numel % 4) { set_error("%s: numel must be a multiple of 4 (pad the buffer)", who); return 1; }
     if (!multicast_buffer || (reinterpret_cast<size_t>(multicast_buffer) & 15)) { set_error("%s: multicast address null or not 16-byte aligned", who); return 1; }
-    allreduce_multimem_kernel<<<148 * AR_G, AR_THREADS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+    // development knobs (read once): HTGS_AR_GRID = CTAs per SM, HTGS_AR_THREADS = threads per CTA (<= 512)
+    static int grid_mul = 0, threads = 0;
+    if (grid_mul == 0) {
+        const char* g = getenv("HTGS_AR_GRID");
+        const char* t = getenv("HTGS_AR_THREADS");
+        grid_mul = g ? std::max(1, atoi(g)) : AR_G;
+        threads = t ? std::min(AR_THREADS, std::max(32, atoi(t))) : AR_THREADS;
+    }
+    allreduce_multimem_kernel<<<148 * grid_mul, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<float4*>(multicast_buffer), rank, world, numel / 4);
     HTGS_LAUNCH_CHECK("allreduce_multimem_kernel");
     return 0;
