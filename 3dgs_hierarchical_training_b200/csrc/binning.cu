@@ -84,17 +84,34 @@ __global__ void tile_ranges_kernel(int64_t R, const uint32_t* __restrict__ R_dev
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= tiles) return;
     if (R_dev) R = min(R, (int64_t)*R_dev);
+    // both lower bounds advance in the same loop, three probes per step each (4-ary search): the kernel is a chain of
+    // dependent L2 round trips, so it pays to keep six independent loads in flight and halve the number of steps
     uint32_t bounds[2];
-#pragma unroll
-    for (int s = 0; s < 2; s++) {
-        const uint64_t target = (uint64_t)(t + s) << 32;
-        int64_t lo = 0, hi = R;  // first index with key >= target
-        while (lo < hi) {
-            const int64_t mid = (lo + hi) >> 1;
-            if (__ldg(keys + mid) < target) lo = mid + 1; else hi = mid;
+    const uint64_t target0 = (uint64_t)t << 32, target1 = (uint64_t)(t + 1) << 32;
+    int64_t lo0 = 0, hi0 = R, lo1 = 0, hi1 = R;  // first index with key >= target lies in [lo, hi]
+    while (lo0 < hi0 || lo1 < hi1) {
+        const int64_t q0 = (hi0 - lo0) >> 2, q1 = (hi1 - lo1) >> 2;
+        const int64_t a0 = lo0 + q0, b0 = lo0 + ((hi0 - lo0) >> 1), c0 = hi0 - 1 - q0;
+        const int64_t a1 = lo1 + q1, b1 = lo1 + ((hi1 - lo1) >> 1), c1 = hi1 - 1 - q1;
+        const bool go0 = lo0 < hi0, go1 = lo1 < hi1;
+        uint64_t ka0 = 0, kb0 = 0, kc0 = 0, ka1 = 0, kb1 = 0, kc1 = 0;
+        if (go0) { ka0 = __ldg(keys + a0); kb0 = __ldg(keys + b0); kc0 = __ldg(keys + c0); }
+        if (go1) { ka1 = __ldg(keys + a1); kb1 = __ldg(keys + b1); kc1 = __ldg(keys + c1); }
+        if (go0) {  // a0 <= b0 <= c0 < hi0
+            if (ka0 >= target0) hi0 = a0;
+            else if (kb0 >= target0) { lo0 = a0 + 1; hi0 = b0; }
+            else if (kc0 >= target0) { lo0 = b0 + 1; hi0 = c0; }
+            else lo0 = c0 + 1;
         }
-        bounds[s] = (uint32_t)lo;
+        if (go1) {
+            if (ka1 >= target1) hi1 = a1;
+            else if (kb1 >= target1) { lo1 = a1 + 1; hi1 = b1; }
+            else if (kc1 >= target1) { lo1 = b1 + 1; hi1 = c1; }
+            else lo1 = c1 + 1;
+        }
     }
+    bounds[0] = (uint32_t)lo0;
+    bounds[1] = (uint32_t)lo1;
     ranges[t] = bounds[0] == bounds[1] ? make_uint2(0, 0) : make_uint2(bounds[0], bounds[1]);
 }
 

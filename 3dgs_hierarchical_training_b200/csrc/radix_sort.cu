@@ -21,7 +21,10 @@ constexpr int SORT_IPT = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_IPT;  // 4096 keys per CTA
 constexpr int SORT_RADIX = 256;
 constexpr int SORT_MAX_PASSES = 8;
-constexpr int SORT_LOOK = 8;  // predecessor status words fetched per look-back round trip
+constexpr int SORT_LOOK = 8;
+#ifndef HTGS_HIST_GRID
+#define HTGS_HIST_GRID 4
+#endif  // predecessor status words fetched per look-back round trip
 
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_PREFIX = 2u << 30;
@@ -64,12 +67,19 @@ sort_hist_kernel(const uint64_t* __restrict__ keys, int64_t n, const uint32_t* _
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += SORT_THREADS) s_hist[i] = 0;
     __syncthreads();
     const int64_t stride = (int64_t)gridDim.x * SORT_THREADS;
-    for (int64_t i = (int64_t)blockIdx.x * SORT_THREADS + threadIdx.x; i < n; i += stride) {
-        const uint64_t k = keys[i];
-        for (int p = 0; p < passes; p++) {
-            const int nb = min(8, end_bit - 8 * p);
-            const uint32_t d = (uint32_t)(k >> (8 * p)) & ((1u << nb) - 1u);
-            atomicAdd(&s_hist[p * SORT_RADIX + d], 1u);
+    constexpr int HU = 4;  // keys in flight per thread
+    for (int64_t i0 = (int64_t)blockIdx.x * SORT_THREADS + threadIdx.x; i0 < n; i0 += stride * HU) {
+        uint64_t k[HU];
+#pragma unroll
+        for (int u = 0; u < HU; u++) k[u] = (i0 + u * stride < n) ? keys[i0 + u * stride] : 0ull;
+#pragma unroll
+        for (int u = 0; u < HU; u++) {
+            if (i0 + u * stride >= n) break;
+            for (int p = 0; p < passes; p++) {
+                const int nb = min(8, end_bit - 8 * p);
+                const uint32_t d = (uint32_t)(k[u] >> (8 * p)) & ((1u << nb) - 1u);
+                atomicAdd(&s_hist[p * SORT_RADIX + d], 1u);
+            }
         }
     }
     __syncthreads();
@@ -275,7 +285,7 @@ int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t*
     SortScratch s = carve(scratch, n);
     const size_t zero_bytes = header_bytes() + (size_t)passes * tiles * SORT_RADIX * sizeof(uint32_t);
     HTGS_CUDA_CHECK(cudaMemsetAsync(scratch, 0, zero_bytes, st));
-    const int hist_blocks = (int)std::min<int64_t>(tiles, 148 * 8);
+    const int hist_blocks = (int)std::min<int64_t>(tiles, 148 * HTGS_HIST_GRID);
     sort_hist_kernel<<<hist_blocks, SORT_THREADS, 0, st>>>(k_in, n, n_dev, end_bit, passes, s.hist);
     HTGS_LAUNCH_CHECK("sort_hist_kernel");
     sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, st>>>(s.hist);
