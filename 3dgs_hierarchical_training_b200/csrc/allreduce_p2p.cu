@@ -10,7 +10,7 @@
 #include "../../include/htgs.h"
 #include "common.cuh"
 #include <algorithm>
-#include <cstdlib>
+#include <atomic>
 
 namespace htgs {
 
@@ -99,9 +99,22 @@ allreduce_two_shot_kernel(const __grid_constant__ PeerPtrs bufs, int rank, long 
     }
 }
 
+// launch shape of the multicast kernel; changed only through htgs_allreduce_set_launch_shape (tuning aid)
+static std::atomic<int> g_mc_ctas_per_sm{AR_G}, g_mc_threads{AR_THREADS};
+
 }  // namespace htgs
 
 using namespace htgs;
+
+extern "C" int htgs_allreduce_set_launch_shape(int ctas_per_sm, int threads) {
+    if (ctas_per_sm < 1 || ctas_per_sm > 16 || threads < 32 || threads > AR_THREADS || (threads & 31)) {
+        set_error("htgs_allreduce_set_launch_shape: need 1..16 CTAs per SM and 32..%d threads (multiple of 32)", AR_THREADS);
+        return 1;
+    }
+    g_mc_ctas_per_sm.store(ctas_per_sm, std::memory_order_relaxed);
+    g_mc_threads.store(threads, std::memory_order_relaxed);
+    return 0;
+}
 
 extern "C" int htgs_allreduce_p2p(const void* const* peer_buffers, int rank, int world, long long numel, void* stream) {
     const char* who = "htgs_allreduce_p2p";
@@ -138,14 +151,7 @@ extern "C" int htgs_allreduce_multimem(void* multicast_buffer, int rank, int wor
     if (numel <= 0 || world == 1) return 0;
     if (numel % 4) { set_error("%s: numel must be a multiple of 4 (pad the buffer)", who); return 1; }
     if (!multicast_buffer || (reinterpret_cast<size_t>(multicast_buffer) & 15)) { set_error("%s: multicast address null or not 16-byte aligned", who); return 1; }
-    // development knobs (read once): HTGS_AR_GRID = CTAs per SM, HTGS_AR_THREADS = threads per CTA (<= 512)
-    static int grid_mul = 0, threads = 0;
-    if (grid_mul == 0) {
-        const char* g = getenv("HTGS_AR_GRID");
-        const char* t = getenv("HTGS_AR_THREADS");
-        grid_mul = g ? std::max(1, atoi(g)) : AR_G;
-        threads = t ? std::min(AR_THREADS, std::max(32, atoi(t))) : AR_THREADS;
-    }
+    const int grid_mul = g_mc_ctas_per_sm.load(std::memory_order_relaxed), threads = g_mc_threads.load(std::memory_order_relaxed);
     allreduce_multimem_kernel<<<148 * grid_mul, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<float4*>(multicast_buffer), rank, world, numel / 4);
     HTGS_LAUNCH_CHECK("allreduce_multimem_kernel");

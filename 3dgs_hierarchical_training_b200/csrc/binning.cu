@@ -134,15 +134,8 @@ int launch_tile_ranges(int64_t R, const uint32_t* R_dev, int W, int H, const uin
     return 0;
 }
 
-uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
-    uint32_t msb = sizeof(n) * 4;
-    uint32_t step = msb;
-    while (step > 1) {
-        step /= 2;
-        if (n >> msb) msb += step; else msb -= step;
-    }
-    if (n >> msb) msb++;
-    return msb;
-}
+// Number of bits needed to write n (at least 1): the tile-id part of the sort key occupies bits [32, 32 + this),
+// the same bit count the reference derives for its CUB call (rasterizer_impl.cu:301).
+uint32_t higher_msb(uint32_t n) { return n ? 32u - (uint32_t)__builtin_clz(n) : 1u; }
 
 }  // namespace htgs

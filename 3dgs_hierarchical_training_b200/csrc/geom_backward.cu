@@ -128,15 +128,32 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
     const float T00 = e.T00, T01 = e.T01, T02 = e.T02, T10 = e.T10, T11 = e.T11, T12 = e.T12;
     float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (denom2inv != 0.f) {
-        dL_da = denom2inv * (-c * c * dcx + 2 * b * c * dcy + (denom - a * c) * dcz);
-        dL_dc = denom2inv * (-a * a * dcz + 2 * a * b * dcy + (denom - a * c) * dcx);
-        dL_db = denom2inv * 2 * (b * c * dcx - (denom + 2 * b * b) * dcy + a * b * dcz);
-        dcov[0] = (T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc);
-        dcov[3] = (T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc);
-        dcov[5] = (T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc);
-        dcov[1] = 2 * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2 * T10 * T11 * dL_dc;
-        dcov[2] = 2 * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2 * T10 * T12 * dL_dc;
-        dcov[4] = 2 * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2 * T11 * T12 * dL_dc;
+        // conic = adj(C)/det with adj(C) = K = [[c,-b],[-b,a]], so a perturbation dC moves it by -conic dC conic and
+        // dL/dC = -(K G K)/det^2, G = [[dcx, dcy],[dcy, dcz]] (the pair accumulates the off-diagonal once for both
+        // symmetric entries); 1/det^2 carries the reference's 1e-7 regulariser (backward.cu:203).
+        const float k00 = c, k01 = -b, k11 = a;
+        const float h00 = dcx * k00 + dcy * k01, h01 = dcx * k01 + dcy * k11;  // H = G K
+        const float h10 = dcy * k00 + dcz * k01, h11 = dcy * k01 + dcz * k11;
+        dL_da = -denom2inv * (k00 * h00 + k01 * h10);                          // -(K H)_00
+        dL_dc = -denom2inv * (k01 * h01 + k11 * h11);                          // -(K H)_11
+        dL_db = -2.f * denom2inv * (k00 * h01 + k01 * h11);                    // both off-diagonal entries
+        // C = T Sigma T^T restricted to rows t0, t1 of T:  dL/dSigma = t0 p^T + t1 r^T with
+        // p = dL_da t0 + (dL_db/2) t1,  r = (dL_db/2) t0 + dL_dc t1  (symmetric); the packed gradient holds the
+        // diagonal once and each off-diagonal pair summed.
+        const float t0[3] = {T00, T01, T02}, t1[3] = {T10, T11, T12};
+        const float hb = 0.5f * dL_db;
+        float pv[3], rv[3];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            pv[j] = dL_da * t0[j] + hb * t1[j];
+            rv[j] = hb * t0[j] + dL_dc * t1[j];
+        }
+        dcov[0] = t0[0] * pv[0] + t1[0] * rv[0];
+        dcov[3] = t0[1] * pv[1] + t1[1] * rv[1];
+        dcov[5] = t0[2] * pv[2] + t1[2] * rv[2];
+        dcov[1] = 2.f * (t0[0] * pv[1] + t1[0] * rv[1]);
+        dcov[2] = 2.f * (t0[0] * pv[2] + t1[0] * rv[2]);
+        dcov[4] = 2.f * (t0[1] * pv[2] + t1[1] * rv[2]);
     }
     // rows of Vrk * T[0] and Vrk * T[1]
     const float vt0x = T00 * c3[0] + T01 * c3[1] + T02 * c3[2];
@@ -221,49 +238,51 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
             for (int k = 0; k < 16; k++)
                 if (k < nact) sd[k] = sh[3 * k] * r0 + sh[3 * k + 1] * r1 + sh[3 * k + 2] * r2;
         }
-#define SHDOT(k) (sd[k])
+        // Basis values w[k] (what dL/dsh_k is proportional to) and the gradient with respect to the view direction.
+        // The direction gradient is sum_k t_k * grad B_k(x,y,z) with t_k = C_k (sh_k . dL/dRGB); the B_k are the
+        // degree-1..3 polynomials of the real SH basis, so the sum is collected monomial by monomial of grad B_k
+        // instead of basis function by basis function.  t_k stays 0 above the active degree.
+        float t[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) t[k] = 0.f;
         w[0] = HTGS_SH_C0;
         int ncoef = 1;
         if (D > 0) {
             ncoef = 4;
             w[1] = -HTGS_SH_C1 * y; w[2] = HTGS_SH_C1 * z; w[3] = -HTGS_SH_C1 * x;
-            ddx = -HTGS_SH_C1 * SHDOT(3);
-            ddy = -HTGS_SH_C1 * SHDOT(1);
-            ddz = HTGS_SH_C1 * SHDOT(2);
+            t[1] = -HTGS_SH_C1 * sd[1]; t[2] = HTGS_SH_C1 * sd[2]; t[3] = -HTGS_SH_C1 * sd[3];
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            const float xx_m_yy = xx - yy, zz4_m_r = 4.f * zz - xx - yy;  // recurring factors of the degree-2/3 basis
             if (D > 1) {
                 ncoef = 9;
-                const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
                 w[4] = HTGS_SH_C2_0 * xy; w[5] = HTGS_SH_C2_1 * yz; w[6] = HTGS_SH_C2_2 * (2.f * zz - xx - yy);
-                w[7] = HTGS_SH_C2_3 * xz; w[8] = HTGS_SH_C2_4 * (xx - yy);
-                const float s4 = SHDOT(4), s5 = SHDOT(5), s6 = SHDOT(6), s7 = SHDOT(7), s8 = SHDOT(8);
-                ddx += HTGS_SH_C2_0 * y * s4 + HTGS_SH_C2_2 * 2.f * -x * s6 + HTGS_SH_C2_3 * z * s7 + HTGS_SH_C2_4 * 2.f * x * s8;
-                ddy += HTGS_SH_C2_0 * x * s4 + HTGS_SH_C2_1 * z * s5 + HTGS_SH_C2_2 * 2.f * -y * s6 + HTGS_SH_C2_4 * 2.f * -y * s8;
-                ddz += HTGS_SH_C2_1 * y * s5 + HTGS_SH_C2_2 * 2.f * 2.f * z * s6 + HTGS_SH_C2_3 * x * s7;
-                if (D > 2) {
-                    ncoef = 16;
-                    w[9] = HTGS_SH_C3_0 * y * (3.f * xx - yy);
-                    w[10] = HTGS_SH_C3_1 * xy * z;
-                    w[11] = HTGS_SH_C3_2 * y * (4.f * zz - xx - yy);
-                    w[12] = HTGS_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                    w[13] = HTGS_SH_C3_4 * x * (4.f * zz - xx - yy);
-                    w[14] = HTGS_SH_C3_5 * z * (xx - yy);
-                    w[15] = HTGS_SH_C3_6 * x * (xx - 3.f * yy);
-                    const float s9 = SHDOT(9), s10 = SHDOT(10), s11 = SHDOT(11), s12 = SHDOT(12), s13 = SHDOT(13),
-                                s14 = SHDOT(14), s15 = SHDOT(15);
-                    ddx += HTGS_SH_C3_0 * s9 * 3.f * 2.f * xy + HTGS_SH_C3_1 * s10 * yz + HTGS_SH_C3_2 * s11 * -2.f * xy +
-                           HTGS_SH_C3_3 * s12 * -3.f * 2.f * xz + HTGS_SH_C3_4 * s13 * (-3.f * xx + 4.f * zz - yy) +
-                           HTGS_SH_C3_5 * s14 * 2.f * xz + HTGS_SH_C3_6 * s15 * 3.f * (xx - yy);
-                    ddy += HTGS_SH_C3_0 * s9 * 3.f * (xx - yy) + HTGS_SH_C3_1 * s10 * xz +
-                           HTGS_SH_C3_2 * s11 * (-3.f * yy + 4.f * zz - xx) + HTGS_SH_C3_3 * s12 * -3.f * 2.f * yz +
-                           HTGS_SH_C3_4 * s13 * -2.f * xy + HTGS_SH_C3_5 * s14 * -2.f * yz +
-                           HTGS_SH_C3_6 * s15 * -3.f * 2.f * xy;
-                    ddz += HTGS_SH_C3_1 * s10 * xy + HTGS_SH_C3_2 * s11 * 4.f * 2.f * yz +
-                           HTGS_SH_C3_3 * s12 * 3.f * (2.f * zz - xx - yy) + HTGS_SH_C3_4 * s13 * 4.f * 2.f * xz +
-                           HTGS_SH_C3_5 * s14 * (xx - yy);
-                }
+                w[7] = HTGS_SH_C2_3 * xz; w[8] = HTGS_SH_C2_4 * xx_m_yy;
+                t[4] = HTGS_SH_C2_0 * sd[4]; t[5] = HTGS_SH_C2_1 * sd[5]; t[6] = HTGS_SH_C2_2 * sd[6];
+                t[7] = HTGS_SH_C2_3 * sd[7]; t[8] = HTGS_SH_C2_4 * sd[8];
             }
+            if (D > 2) {
+                ncoef = 16;
+                w[9] = HTGS_SH_C3_0 * y * (3.f * xx - yy);
+                w[10] = HTGS_SH_C3_1 * xy * z;
+                w[11] = HTGS_SH_C3_2 * y * zz4_m_r;
+                w[12] = HTGS_SH_C3_3 * z * (2.f * zz - 3.f * (xx + yy));
+                w[13] = HTGS_SH_C3_4 * x * zz4_m_r;
+                w[14] = HTGS_SH_C3_5 * z * xx_m_yy;
+                w[15] = HTGS_SH_C3_6 * x * (xx - 3.f * yy);
+                t[9] = HTGS_SH_C3_0 * sd[9]; t[10] = HTGS_SH_C3_1 * sd[10]; t[11] = HTGS_SH_C3_2 * sd[11];
+                t[12] = HTGS_SH_C3_3 * sd[12]; t[13] = HTGS_SH_C3_4 * sd[13]; t[14] = HTGS_SH_C3_5 * sd[14];
+                t[15] = HTGS_SH_C3_6 * sd[15];
+            }
+            // d/dx: linear part, then the monomials 1, x, y, z, xy, yz, xz, and the two quadratic forms
+            ddx = t[3] + y * t[4] + z * t[7] + 2.f * x * (t[8] - t[6])
+                + xy * (6.f * t[9] - 2.f * t[11]) + yz * t[10] + xz * (2.f * t[14] - 6.f * t[12])
+                + t[13] * (zz4_m_r - 2.f * xx) + 3.f * t[15] * xx_m_yy;
+            ddy = t[1] + x * t[4] + z * t[5] - 2.f * y * (t[6] + t[8])
+                + 3.f * t[9] * xx_m_yy + xz * t[10] + t[11] * (zz4_m_r - 2.f * yy)
+                - yz * (6.f * t[12] + 2.f * t[14]) - xy * (2.f * t[13] + 6.f * t[15]);
+            ddz = t[2] + y * t[5] + 4.f * z * t[6] + x * t[7]
+                + xy * t[10] + 8.f * (yz * t[11] + xz * t[13]) + 3.f * t[12] * (2.f * zz - xx - yy) + t[14] * xx_m_yy;
         }
-#undef SHDOT
         float* o = dL_dsh + (size_t)idx * M * 3;
         if (RAW) {
 #pragma unroll
@@ -303,42 +322,42 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
         dmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
     }
 
-    // ---- scale / rotation backward, backward.cu:278-341 ----
+    // ---- scale / rotation backward (what backward.cu:278-341 computes) ----
+    // Sigma = L L^T with L = Rm diag(s), Rm the rotation matrix of the (un-normalised) quaternion and
+    // s = scale_modifier * scale.  With dS the symmetric matrix form of the packed dL/dSigma (off-diagonals halved),
+    //   dL/dL = 2 dS L,   dL/ds_j = sum_i (dL/dL)_ij Rm_ij,   H = dL/dRm = (dL/dL) diag(s).
+    // Rm = (1 - 2|v|^2) I + 2 v v^T + 2 r [v]x  for q = (r, v), hence
+    //   dL/dr = 2 v . a,   dL/dv = 2 r a + 2 (H + H^T) v - 4 tr(H) v,   a = axial vector of H - H^T.
+    // Like the reference, dL/dscale is the derivative with respect to s (the scale_modifier factor is not applied).
     if (scales != nullptr) {
         const float r = q.x, x = q.y, y = q.z, z = q.w;
-        // R[c][i]: glm column c, row i
-        const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
-                               {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
-                               {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+        const float Rm[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                                {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                                {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
         const float s[3] = {scale_modifier * sc0, scale_modifier * sc1, scale_modifier * sc2};
         const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
                                 {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
                                 {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
-        float dMt[3][3];  // dL_dMt[c][i] = dL_dM[i][c],  dL_dM = 2*M*dL_dSigma, M[c][i] = s[i]*R[c][i]
+        float Hm[3][3];
+        float dsc[3] = {0.f, 0.f, 0.f};
 #pragma unroll
-        for (int cc = 0; cc < 3; cc++)
+        for (int i = 0; i < 3; i++)
 #pragma unroll
-            for (int i = 0; i < 3; i++) {
-                float acc = 0.f;
-#pragma unroll
-                for (int k = 0; k < 3; k++) acc += (2.0f * s[i] * R[k][i]) * dS[cc][k];
-                dMt[i][cc] = acc;
+            for (int j = 0; j < 3; j++) {
+                const float gl = 2.f * s[j] * (dS[i][0] * Rm[0][j] + dS[i][1] * Rm[1][j] + dS[i][2] * Rm[2][j]);  // (dL/dL)_ij
+                dsc[j] += gl * Rm[i][j];
+                Hm[i][j] = gl * s[j];
             }
-        float dsc[3];
-#pragma unroll
-        for (int cc = 0; cc < 3; cc++) dsc[cc] = R[0][cc] * dMt[cc][0] + R[1][cc] * dMt[cc][1] + R[2][cc] * dMt[cc][2];
-#pragma unroll
-        for (int cc = 0; cc < 3; cc++)
-#pragma unroll
-            for (int i = 0; i < 3; i++) dMt[cc][i] *= s[cc];
+        const float ax = Hm[2][1] - Hm[1][2], ay = Hm[0][2] - Hm[2][0], az = Hm[1][0] - Hm[0][1];
+        const float tr4 = 4.f * (Hm[0][0] + Hm[1][1] + Hm[2][2]);
+        const float hx = 2.f * Hm[0][0] * x + (Hm[0][1] + Hm[1][0]) * y + (Hm[0][2] + Hm[2][0]) * z;  // (H + H^T) v
+        const float hy = (Hm[0][1] + Hm[1][0]) * x + 2.f * Hm[1][1] * y + (Hm[1][2] + Hm[2][1]) * z;
+        const float hz = (Hm[0][2] + Hm[2][0]) * x + (Hm[1][2] + Hm[2][1]) * y + 2.f * Hm[2][2] * z;
         float4 dq;
-        dq.x = 2 * z * (dMt[0][1] - dMt[1][0]) + 2 * y * (dMt[2][0] - dMt[0][2]) + 2 * x * (dMt[1][2] - dMt[2][1]);
-        dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) -
-               4 * x * (dMt[2][2] + dMt[1][1]);
-        dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) -
-               4 * y * (dMt[2][2] + dMt[0][0]);
-        dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) -
-               4 * z * (dMt[1][1] + dMt[0][0]);
+        dq.x = 2.f * (x * ax + y * ay + z * az);
+        dq.y = 2.f * (r * ax + hx) - tr4 * x;
+        dq.z = 2.f * (r * ay + hy) - tr4 * y;
+        dq.w = 2.f * (r * az + hz) - tr4 * z;
         if (RAW) {
             // exp backward; F.normalize backward: (g - qhat (qhat . g)) / n
             dsc[0] *= sc0; dsc[1] *= sc1; dsc[2] *= sc2;

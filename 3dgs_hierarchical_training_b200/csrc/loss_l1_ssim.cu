@@ -10,6 +10,7 @@
 // reads 2 images and writes 3 maps, backward reads 3 maps + 2 images and writes 1 image (8*C*H*W*4 B total).
 #include "../../include/htgs.h"
 #include "common.cuh"
+#include <mutex>
 
 namespace htgs {
 
@@ -244,15 +245,21 @@ ssim_backward_kernel(int C, int H, int W, const float* __restrict__ pred, const 
     }
 }
 
+// The 11 window taps live in __constant__ memory and are uploaded once per device, under a lock (host threads may
+// race to the first call).  The upload is a blocking cudaMemcpyToSymbol: the first htgs_l1_ssim_* call on a device
+// must therefore come outside any stream capture (documented in include/htgs.h).
 static bool g_win_set[64] = {};
+static std::mutex g_win_mutex;
 static int ensure_window() {
     int dev = 0;
     HTGS_CUDA_CHECK(cudaGetDevice(&dev));
-    if (!g_win_set[dev & 63]) {
+    if (dev < 0 || dev >= 64) { set_error("htgs_l1_ssim: device ordinal %d not supported (max 63)", dev); return 1; }
+    std::lock_guard<std::mutex> lock(g_win_mutex);
+    if (!g_win_set[dev]) {
         float w[11];
         win_host(w);
         HTGS_CUDA_CHECK(cudaMemcpyToSymbol(c_win, w, sizeof(w)));
-        g_win_set[dev & 63] = true;
+        g_win_set[dev] = true;
     }
     return 0;
 }

@@ -34,7 +34,6 @@ constexpr uint32_t VALUE_MASK = ~FLAG_MASK;
 struct SortScratch {
     uint32_t* hist;     // [SORT_MAX_PASSES][256]
     uint32_t* tickets;  // [SORT_MAX_PASSES]
-    uint32_t* error;    // [1]
     uint32_t* status;   // [passes][tiles][256]
 };
 
@@ -53,7 +52,6 @@ static SortScratch carve(void* scratch, int64_t n) {
     char* p = reinterpret_cast<char*>(scratch);
     s.hist = reinterpret_cast<uint32_t*>(p);
     s.tickets = s.hist + SORT_MAX_PASSES * SORT_RADIX;
-    s.error = s.tickets + SORT_MAX_PASSES;
     s.status = reinterpret_cast<uint32_t*>(p + header_bytes());
     (void)n;
     return s;
@@ -119,7 +117,7 @@ __global__ void __launch_bounds__(SORT_RADIX) sort_scan_hist_kernel(uint32_t* __
 __global__ void __launch_bounds__(SORT_THREADS, 3)
 onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
                 uint32_t* __restrict__ vout, int64_t n, const uint32_t* __restrict__ n_dev, int shift, int nbits,
-                const uint32_t* __restrict__ digit_start, uint32_t* status, uint32_t* ticket, uint32_t* error) {
+                const uint32_t* __restrict__ digit_start, uint32_t* status, uint32_t* ticket) {
     __shared__ uint64_t s_keys[SORT_TILE];
     __shared__ uint8_t s_digit[SORT_TILE];
     __shared__ uint32_t s_whist[SORT_WARPS][SORT_RADIX];
@@ -208,7 +206,10 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
             }
             if (found) break;
             if (used == 0) {
-                if (++spins > (1u << 24)) { atomicExch(error, 1u); break; }  // never hang the GPU
+                if (++spins > (1u << 24)) {  // a predecessor never published: stop the grid loudly, never hang the GPU
+                    printf("htgs: radix sort look-back timed out (tile %u, digit %d)\n", tile, tid);
+                    __trap();  // the launch fails; the caller sees a CUDA error at its next synchronisation
+                }
                 __nanosleep(32);
             } else {
                 spins = 0;
@@ -256,13 +257,6 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
     }
 }
 
-__global__ void sort_check_error_kernel(const uint32_t* error) {
-    if (*error) {
-        printf("htgs: radix sort look-back timed out\n");
-        __trap();
-    }
-}
-
 // Sorts on key bits [0, end_bit).  With n_dev != nullptr the element count is read on the device
 // (min(n, *n_dev)); n is then only the capacity the grid and the scratch were sized for, which lets
 // the caller enqueue the sort before the count has reached the host.  After the call the sorted pairs are in
@@ -295,7 +289,7 @@ int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t*
         const int nbits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
         onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, st>>>(ka, va, kb, vb, n, n_dev, 8 * p, nbits, s.hist + p * SORT_RADIX,
                                                                    s.status + (size_t)p * tiles * SORT_RADIX,
-                                                                   s.tickets + p, s.error);
+                                                                   s.tickets + p);
         HTGS_LAUNCH_CHECK("onesweep_kernel");
         uint64_t* tk = ka; ka = kb; kb = tk;
         uint32_t* tv = va; va = vb; vb = tv;

@@ -18,7 +18,10 @@
 //     (different streams, or different host threads) would overwrite each other's counters:
 //     keep calls on one device ordered;
 //   * the first call on each device resolves the array's device address (no allocation, but a
-//     one-off runtime query); make that first call outside any stream capture.
+//     one-off runtime query); make that first call outside any stream capture.  The address is
+//     remembered per device ordinal for the life of the process: after cudaDeviceReset() the
+//     library image is reloaded and the remembered address is stale, so a process that resets a
+//     device must not call this entry point on it again.
 #include "../../include/htgs.h"
 #include "common.cuh"
 #include <mutex>
@@ -50,9 +53,13 @@ int scratch_for_current_device(void** out) {
     if (g_scratch_addr[dev] == nullptr) {
         void* p = nullptr;
         e = cudaGetSymbolAddress(&p, g_sort_static_scratch);
-        if (e != cudaSuccess || p == nullptr) {
+        if (e != cudaSuccess) {
             htgs::set_error("htgs_sort_pairs_static: cudaGetSymbolAddress failed on device %d: %s", dev,
                             cudaGetErrorString(e));
+            return 1;
+        }
+        if (p == nullptr) {
+            htgs::set_error("htgs_sort_pairs_static: cudaGetSymbolAddress returned a null address on device %d", dev);
             return 1;
         }
         g_scratch_addr[dev] = p;

@@ -17,6 +17,14 @@ NUM_CHANNELS = 3  # cuda_rasterizer/config.h:15
 # Speculative sizing of the binning buffer (htgs_forward_render_capacity): the previous call's R for the
 # same (device, P, W, H) predicts the next one, so the whole forward is enqueued without the host
 # waiting for R; the exact R is read afterwards while the GPU is already blending.
+#
+# This is the one piece of process-global state of the plugin mirror: `_R_PREDICTION` (a dict keyed by
+# (device, P, W, H)) and ONE pinned 4-byte counter per device (`_PINNED_R`) that the async preprocess writes R into.
+# A forward reads its own R back from that counter before it returns, so forwards issued one after another from one
+# host thread -- the reference trainer's pattern -- are safe on any stream.  Two forwards IN FLIGHT at the same time on
+# one device (two host threads, or two streams driven without waiting for the first call to return) would share the
+# counter and may read each other's R: give each thread its own process, or set SPECULATIVE = False (the reference's
+# blocking two-phase flow, no shared state).
 _R_PREDICTION = {}
 _PINNED_R = {}
 SPECULATIVE = True
@@ -30,22 +38,30 @@ CAPACITY_MARGIN = 1.25
 _GRAD_ARENA = None
 
 
-def set_grad_arena(flat, slices):
+def set_grad_arena(flat, slices, owners=None):
     """flat: 1-D float32 CUDA tensor; slices: {"means3D"|"shs"|"opacities"|"scales"|"rotations": (lo, hi)}.
+    owners (optional): {name: leaf tensor whose .grad adopts the slice}.  When a leaf still holds last step's
+    arena slice as its .grad (zero_grad(set_to_none=False), or a second view rendered before the optimizer step) the
+    backward must not overwrite that memory: autograd would then add the new gradient to itself.  With owners given,
+    such a backward gets ordinary fresh tensors and autograd accumulates them INTO the arena slice, which is the
+    correct sum.  Without owners the caller promises one backward per parameter per step and .grad = None in between.
     Pass (None, None) to clear."""
     global _GRAD_ARENA
-    _GRAD_ARENA = None if flat is None else (flat, dict(slices))
+    _GRAD_ARENA = None if flat is None else (flat, dict(slices), dict(owners) if owners else None)
 
 
 def _arena_or_empty(name, shape, **opts):
     if _GRAD_ARENA is not None:
-        flat, slices = _GRAD_ARENA
+        flat, slices, owners = _GRAD_ARENA
         rng = slices.get(name)
         n = 1
         for v in shape:
             n *= v
         if rng is not None and rng[1] - rng[0] == n and flat.device == opts["device"]:
-            return flat[rng[0]:rng[1]].view(shape)  # a fresh view object: autograd may adopt it as .grad
+            owner = owners.get(name) if owners else None
+            held = owner is not None and owner.grad is not None and owner.grad.data_ptr() == flat.data_ptr() + 4 * rng[0]
+            if not held:
+                return flat[rng[0]:rng[1]].view(shape)  # a fresh view object: autograd may adopt it as .grad
     return torch.empty(shape, **opts)
 
 

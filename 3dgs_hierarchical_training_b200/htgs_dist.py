@@ -45,7 +45,8 @@ class FlatGradReducer:
             buf.zero_()
             off = buf.data_ptr() - int(hdl.buffer_ptrs[hdl.rank])
             table = (ctypes.c_void_p * hdl.world_size)(*[int(p) + off for p in hdl.buffer_ptrs])
-            mc = int(hdl.multicast_ptr) if getattr(hdl, "has_multicast_support", lambda *a: False) and hdl.multicast_ptr else 0
+            # a handle without NVSwitch multicast reports multicast_ptr == 0; that address is the only capability gate
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
             self._peer = dict(buf=buf, hdl=hdl, table=table, n_pad=n_pad, mc=(mc + off) if mc else 0)
             # peer loads move 2(N-1)/N buffers per link direction, the switch multicast about one: NVLS from 3 ranks up
             self.collective = "multimem" if (mc and hdl.world_size > 2 and peer_memory != "p2p") or peer_memory == "multimem" else "p2p"
@@ -61,11 +62,15 @@ class FlatGradReducer:
             o += P * per
         assert o == self.flat.numel()
 
-    def install_arena(self):
+    def install_arena(self, params=None):
         """Let the rasterizer backward write its gradients directly into this buffer (no pack copy).
-        Valid when each parameter gets exactly one backward per step."""
+
+        The backward OVERWRITES the slice, so it is only right when the slice is not still some parameter's live .grad:
+        one backward per parameter per step, and `.grad = None` / `zero_grad(set_to_none=True)` between steps.  Pass
+        `params` ({name in PARAM_ORDER: leaf tensor handed to the rasterizer}) to have that checked on every backward:
+        a parameter that still holds its arena slice gets an ordinary accumulate instead (correct, one extra add)."""
         from diff_gaussian_rasterization import _C
-        _C.set_grad_arena(self.flat, self.slices)
+        _C.set_grad_arena(self.flat, self.slices, params)
 
     @staticmethod
     def remove_arena():

@@ -63,6 +63,7 @@ _SIGNATURES = {
     "htgs_mark_visible": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_allreduce_p2p": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, ctypes.c_longlong, c_void_p]),
     "htgs_allreduce_multimem": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p]),
+    "htgs_allreduce_set_launch_shape": (c_int, [c_int, c_int]),
     "htgs_row_scan_scratch_bytes": (c_size_t, [c_int]),
     "htgs_row_scan": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_rows_compact": (c_int, [c_int, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),

@@ -21,8 +21,15 @@
  *   - matrices use the reference's row-vector convention (flat m[4*c+r]);
  *   - optional inputs are NULL exactly where the reference passes an empty
  *     tensor (data_ptr()==0);
- *   - no global mutable state; re-entrant per (device, stream).  Work buffers
- *     are caller-owned; their sizes come from the *_bytes() queries.
+ *   - work buffers are caller-owned; their sizes come from the *_bytes() queries.
+ *     The rasterizer, sort, knn, optimizer and row-surgery entry points keep no
+ *     state between calls and are re-entrant per (device, stream).  The
+ *     exceptions, each documented at its declaration: the built-in scratch
+ *     array of htgs_sort_pairs_static (shared per device), the SSIM window
+ *     constants of htgs_l1_ssim_* (uploaded once per device under a lock, first
+ *     call outside stream capture), the launch-shape override of
+ *     htgs_allreduce_set_launch_shape, and the htgs_profile_* stage timers
+ *     (process-wide measurement aid, not thread-safe).
  */
 #ifndef HTGS_H_INCLUDED
 #define HTGS_H_INCLUDED
@@ -175,7 +182,8 @@ int htgs_sort_pairs(int64_t n, int end_bit, uint64_t* keys_in, uint32_t* values_
  *     what the previous call left behind is harmless, but calls whose GPU work overlaps (other
  *     streams, other host threads) corrupt each other: keep them ordered;
  *   - the first call on each device looks up the array's device address; issue that first call
- *     outside any stream capture.
+ *     outside any stream capture.  The address is cached per device for the life of the process
+ *     (do not use this entry point on a device after cudaDeviceReset).
  * Same contract as htgs_sort_pairs otherwise (stable, key bits [0,end_bit), inputs clobbered). */
 #define HTGS_SORT_STATIC_MAX_PAIRS (1LL << 20)
 #define HTGS_SORT_STATIC_SCRATCH_BYTES 2105856
@@ -235,6 +243,9 @@ int htgs_allreduce_p2p(const void* const* peer_buffers, int rank, int world, lon
  * replicates the store (multimem.st), so each GPU moves about one buffer per direction at any world size.  The
  * summation order inside the switch is the hardware's; all ranks still receive the same bits. */
 int htgs_allreduce_multimem(void* multicast_buffer, int rank, int world, long long numel, void* stream);
+/* Tuning aid for htgs_allreduce_multimem: CTAs per SM (1..16, default 2) and threads per CTA (32..512, default 512)
+ * of its kernel, process-wide.  Measured flat on 4 and 8 B200s (0.57-0.60 ms for 236 MB at every shape). */
+int htgs_allreduce_set_launch_shape(int ctas_per_sm, int threads);
 
 /* ---- row surgery for prune / clone (first half; opt-in) ----
  * Replaces the per-tensor boolean-mask indexing of _prune_optimizer / prune_points and the per-tensor
@@ -301,7 +312,9 @@ int htgs_backward_raw(int P, int D, int64_t R, int W, int H, const float* backgr
  * trainer/losses.py:98-136 (SSIM: 11x11 sigma-1.5 window, zero padding, per channel, :147-200), for
  * pred/gt float32 [C,H,W].  forward writes out3 = {loss, l1, 1-ssim} (device) and, when dmaps != NULL,
  * the three derivative maps [3][C][H][W] the backward consumes; backward writes dL_dpred[C,H,W] =
- * grad_loss * dloss/dpred (grad_loss: device scalar, NULL = 1).  scratch from htgs_l1_ssim_scratch_bytes. */
+ * grad_loss * dloss/dpred (grad_loss: device scalar, NULL = 1).  scratch from htgs_l1_ssim_scratch_bytes.
+ * The first call on each device uploads the 11 window taps to constant memory with a blocking copy (under a
+ * lock): make it outside any stream capture. */
 size_t htgs_l1_ssim_scratch_bytes(int C, int H, int W);
 int htgs_l1_ssim_forward(int C, int H, int W, const float* pred, const float* gt, float lambda_dssim,
                          float* dmaps, void* scratch, float* out3, void* stream);

@@ -15,6 +15,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 DGR_PATH = os.path.join(_HERE, "_ref", "libref_dgr.so")
 KNN_PATH = os.path.join(_HERE, "_ref", "libref_knn.so")
+CUB_PATH = os.path.join(_HERE, "_ref", "libref_cub.so")
 _dgr = None
 _knn = None
 _p, _i, _f = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
@@ -50,6 +51,39 @@ def knn():
         l.ref_dist2.argtypes = [_i, _p, _p]
         _knn = l
     return _knn
+
+
+_cub = None
+
+
+def cub_available():
+    return os.path.exists(CUB_PATH)
+
+
+def cub():
+    """cub::DeviceRadixSort::SortPairs<u64,u32> as the reference calls it (oracle/ref_shim_cub.cu)."""
+    global _cub
+    if _cub is None:
+        l = ctypes.CDLL(CUB_PATH)
+        l.ref_cub_temp_bytes.restype = ctypes.c_size_t
+        l.ref_cub_temp_bytes.argtypes = [ctypes.c_int64]
+        l.ref_cub_sort_pairs.restype = _i
+        l.ref_cub_sort_pairs.argtypes = [ctypes.c_int64, _i, _p, _p, _p, _p, _p, ctypes.c_size_t]
+        _cub = l
+    return _cub
+
+
+def cub_sort_pairs(keys, values, end_bit, out=None, temp=None):
+    """Sorted copies (keys_out, values_out) of int64 keys / int32 values on bits [0, end_bit); default stream."""
+    n = keys.numel()
+    ko, vo = out if out is not None else (torch.empty_like(keys), torch.empty_like(values))
+    if temp is None:
+        temp = torch.empty(max(1, cub().ref_cub_temp_bytes(n)), dtype=torch.uint8, device=keys.device)
+    rc = cub().ref_cub_sort_pairs(n, end_bit, keys.data_ptr(), values.data_ptr(), ko.data_ptr(), vo.data_ptr(), temp.data_ptr(),
+                                  temp.numel())
+    if rc != 0:
+        raise RuntimeError(f"cub SortPairs failed with CUDA error {rc}")
+    return ko, vo
 
 
 def _ptr(t):

@@ -34,6 +34,7 @@ def _built():
     import __graft_entry__ as g
     lib = os.path.join(ROOT, "3dgs_hierarchical_training_b200", "libhtgs.so")
     orc = os.path.join(ROOT, "oracle", "liborc.so")
-    if not (os.path.exists(lib) and os.path.exists(orc)):
+    stale = importlib.import_module("3dgs_hierarchical_training_b200.build").needs_build()
+    if stale or not (os.path.exists(lib) and os.path.exists(orc)):
         g.build()
     yield

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 import htgs_synthetic as syn
-from helpers import GRAD_RTOL, np_, rel_inf
+from helpers import GRAD_RTOL, np_, rel_inf, run_ours
 from oracle import golden
 
 pytestmark = pytest.mark.gpu
@@ -125,3 +125,65 @@ def test_gradient_arena_is_adopted_and_equal():
         assert rel_inf(views[k], plain[k].grad) <= GRAD_RTOL, k
     again = run()  # arena removed: ordinary allocation again
     assert again["shs"].grad.data_ptr() != red.flat.data_ptr() + 4 * red.slices["shs"][0]
+
+
+def test_gradient_arena_with_live_grad_accumulates_instead_of_overwriting():
+    """A parameter that still holds last step's arena slice as .grad (zero_grad(set_to_none=False), or two views per
+    step) must end with the SUM of both backwards, as plain autograd gives -- not with a gradient added to itself."""
+    import htgs_dist
+    cfg, scene, cam, up, bg, rast = _setup("small")
+    dev = torch.device("cuda:0")
+    p = {k: scene[k].clone().requires_grad_(True) for k in htgs_dist.PARAM_ORDER}
+
+    def backward_once(scale):
+        out = rast(means3D=p["means3D"], means2D=torch.zeros_like(p["means3D"], requires_grad=True), opacities=p["opacities"],
+                   shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+        torch.autograd.backward((out[0], out[2], out[3]), (scale * up["dL_dcolor"], scale * up["dL_ddepth"], scale * up["dL_dalpha"]))
+
+    backward_once(1.0)
+    single = {k: p[k].grad.clone() for k in p}
+    for v in p.values():
+        v.grad = None
+    red = htgs_dist.FlatGradReducer(cfg["P"], dev)
+    red.install_arena(p)
+    try:
+        backward_once(1.0)   # adopted: .grad is the arena slice
+        assert p["shs"].grad.data_ptr() == red.flat.data_ptr() + 4 * red.slices["shs"][0]
+        backward_once(2.0)   # .grad still live: must accumulate 1x + 2x into the same slice
+        assert red.pack_if_needed({k: p[k].grad for k in htgs_dist.PARAM_ORDER}) == 0
+    finally:
+        red.remove_arena()
+    for k in htgs_dist.PARAM_ORDER:
+        assert rel_inf(p[k].grad, 3.0 * single[k]) <= 2 * GRAD_RTOL, k
+
+
+def test_speculative_forward_reruns_when_the_predicted_capacity_is_too_small():
+    """diff_gaussian_rasterization/_C.py sizes the binning buffer from the previous call's R.  Poisoning that
+    prediction far too low forces the overflow branch (phase 2 redone at the exact size); while the undersized
+    attempt runs, the kernels must stay inside the small buffer (guards in make_keys / sort / tile ranges).  The
+    result must be bit-identical to the blocking two-phase flow, forward and backward state included."""
+    from diff_gaussian_rasterization import _C
+    cfg, scene, cam, up = syn.make_config("config1", device="cuda")
+    bg = torch.tensor([0.1, 0.2, 0.3], device="cuda")
+    P, W, H = cfg["P"], cfg["W"], cfg["H"]
+    key = (0, P, W, H)
+    saved = _C.SPECULATIVE
+    try:
+        _C.SPECULATIVE = False
+        exact = run_ours(scene, cam, up, bg)
+        _C.SPECULATIVE = True
+        R = exact["R"]
+        assert R > 16000  # so that capacity = 1.25 * poison + 8192 really is too small below
+        for poison in (R // 8, 1, R):   # far too small, absurdly small, exact (no rerun)
+            _C._R_PREDICTION[key] = poison
+            # canary behind the undersized buffer would be torch's next block; instead check every output bit
+            got = run_ours(scene, cam, up, bg)
+            assert got["R"] == R and _C._R_PREDICTION[key] == R
+            for k in ("color", "depth", "alpha", "radii", "n_contrib", "ranges", "tiles_touched", "point_offsets"):
+                assert torch.equal(got[k], exact[k]), (poison, k)
+            assert torch.equal(got["keys"][:R], exact["keys"][:R]) and torch.equal(got["point_list"][:R], exact["point_list"][:R])
+            for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations", "dL_dmeans2D"):
+                assert rel_inf(got["grads"][k], exact["grads"][k]) <= GRAD_RTOL, (poison, k)
+    finally:
+        _C.SPECULATIVE = saved
+        _C._R_PREDICTION.pop(key, None)

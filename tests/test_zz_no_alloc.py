@@ -71,6 +71,37 @@ def test_static_scratch_sort_equals_allocating_sort_twice_in_a_row():
         assert torch.equal(ko, ks) and torch.equal(vo, order.int())
 
 
+def test_static_scratch_sort_leaves_device_free_memory_unchanged():
+    """The property the entry point exists for: a call takes no device memory, not even transiently.
+    The driver's own free-memory figure (cudaMemGetInfo, which sees every allocation on the device, torch's
+    included) must read the same before and after.  One call is made first and not measured: it is the call
+    that resolves the array's address, and with CUDA's lazy module loading it is also the moment the library
+    image -- the 2 MB array included -- is placed on the device."""
+    lib = nat.lib()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n, end_bit = 200_003, 45
+    keys, vals = _data(n, end_bit, 7)
+    _static_sort(keys, vals, end_bit)  # first use on this device (unmeasured, see above)
+    kin, vin = keys.clone(), vals.clone()
+    ko, vo = torch.empty_like(keys), torch.empty_like(vals)
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info(dev)
+    reserved_before = torch.cuda.memory_reserved(dev)
+    for _ in range(3):
+        nat.check(lib.htgs_sort_pairs_static(n, end_bit, kin.data_ptr(), vin.data_ptr(), ko.data_ptr(), vo.data_ptr(),
+                                             _stream(dev)), "htgs_sort_pairs_static")
+        free_during, _ = torch.cuda.mem_get_info(dev)  # GPU work still in flight
+        assert free_during == free_before
+        kin.copy_(keys)
+        vin.copy_(vals)
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info(dev)
+    assert free_after == free_before, f"device free memory moved by {free_before - free_after} bytes"
+    assert torch.cuda.memory_reserved(dev) == reserved_before  # and torch's caching allocator was not touched either
+    ks, order = torch.sort(keys, stable=True)
+    assert torch.equal(ko, ks) and torch.equal(vo, order.int())
+
+
 def test_static_scratch_sort_refuses_more_than_its_maximum():
     lib = nat.lib()
     n = nat.SORT_STATIC_MAX_PAIRS + 1
