@@ -29,26 +29,29 @@ def rel_inf(a, b):
 #   |g_i - ref_i| <= GRAD_ELEM_RTOL * |ref_i| + GRAD_ELEM_ATOL * ||ref||_inf     for EVERY element.
 # rel_inf alone lets a small-magnitude row be entirely wrong as long as it stays below 1e-4 of the tensor's largest
 # entry; this bar holds an entry 100x smaller than that to 1 % of its own value.  The absolute floor is what the
-# reference's own run-to-run noise needs (its float atomics commit in hardware order): two runs of the reference
-# binary on config 2/3/5 differ by up to ~1e-6 of the tensor scale on individual entries
-# (profiles/r02_grad_self_noise.json, tools/grad_noise.py).
-GRAD_ELEM_RTOL = 1e-2
+# reference's own run-to-run noise needs (its float atomics commit in hardware order).  Measured on the B200
+# (tools/grad_noise.py -> profiles/r02_grad_self_noise.json, configs 2/3/5, all six gradient tensors): two runs of the
+# reference binary reach 0.04 of this bar against each other, this library 0.045 against the reference and 0.006
+# against itself -- a 20x margin over noise, while an entry at 1 % of the tensor's scale is still held to 0.2 %.
+# Against the CPU oracle (whose exp differs from the GPU's ex2.approx by a couple of ulp) the relative part is 1e-2.
+GRAD_ELEM_RTOL = 1e-3
 GRAD_ELEM_ATOL = 1e-5
+ORACLE_GRAD_ELEM_RTOL = 1e-2
 
 
-def elem_excess(a, b):
-    """max_i |a_i - b_i| / (GRAD_ELEM_RTOL |b_i| + GRAD_ELEM_ATOL ||b||_inf); the element-wise bar holds when <= 1."""
+def elem_excess(a, b, rtol=GRAD_ELEM_RTOL, atol=GRAD_ELEM_ATOL):
+    """max_i |a_i - b_i| / (rtol |b_i| + atol ||b||_inf); the element-wise bar holds when <= 1."""
     if hasattr(a, "detach") and hasattr(b, "detach") and a.is_cuda:
         a, b = a.detach().reshape(-1).double(), b.detach().reshape(-1).double().to(a.device)
         if a.numel() == 0:
             return 0.0
         scale = float(b.abs().max().clamp_min(1e-30))
-        return float(((a - b).abs() / (GRAD_ELEM_RTOL * b.abs() + GRAD_ELEM_ATOL * scale)).max())
+        return float(((a - b).abs() / (rtol * b.abs() + atol * scale)).max())
     a, b = np_(a).astype(np.float64).reshape(-1), np_(b).astype(np.float64).reshape(-1)
     if a.size == 0:
         return 0.0
     scale = max(float(np.abs(b).max()), 1e-30)
-    return float((np.abs(a - b) / (GRAD_ELEM_RTOL * np.abs(b) + GRAD_ELEM_ATOL * scale)).max())
+    return float((np.abs(a - b) / (rtol * np.abs(b) + atol * scale)).max())
 
 
 def bits_equal(a, b):
