@@ -1,29 +1,34 @@
 // K5: back-to-front gradient of the tile blend (colour + depth + alpha).
 // Replaces BACKWARD::render / renderCUDA (cuda_rasterizer/backward.cu:415-601).
 //
-// The reference issues 10 global float atomics per blended (pixel, Gaussian)
-// pair (backward.cu:555-598) and is bound by L2 atomic throughput.  Here the 10
-// partial gradients of a Gaussian are
-//   1. summed over the 32 pixels of a warp with a 12-shuffle transpose-reduce
-//      (each halving step swaps half of the remaining values with the partner
-//      lane, so lane pairs end up holding the warp total of one value each),
-//   2. parked in a per-warp shared-memory slot (plain store, no atomics),
-//   3. summed over the tile's 8 warps when the 128-Gaussian batch is done and
-//      sent to HBM as three 128-bit vector reductions per (tile, Gaussian),
-// i.e. 3 vector atomics per tile instance instead of 10 scalar ones per pixel
-// pair.  Per-pixel arithmetic follows the reference (same thresholds, same
-// T = T/(1-alpha) recurrence); only the summation order of the atomics differs.
-// The 8x4 reach masks of blend_common.cuh skip Gaussians that cannot touch a
-// warp's pixels, and whole batches behind the tile's last contributor.
+// The reference issues 10 global float atomics per blended (pixel, Gaussian) pair (backward.cu:555-598).  Here a
+// (tile, Gaussian) instance ends in three 128-bit vector reductions, and the sum over the tile's pixels that precedes
+// them is done in two steps that keep the per-pair instruction count low (the kernel is issue-bound):
 //
-// Instruction economy (the kernel is FP32-issue bound): a lane does not form the five geometric
-// gradients itself.  With w = G * dL/dalpha it only accumulates the moments  w, w*dx, w*dy,
-// w*dx*dx, w*dx*dy, w*dy*dy ; the conic/opacity factors, which are per-Gaussian constants, are
-// applied once per (tile, Gaussian) when the batch is flushed.  Likewise the per-channel
-// "accumulated colour behind me" recurrences of backward.cu:547-567 collapse into one scalar
-// recurrence of their dot product with the pixel's upstream gradient (they only ever enter
-// dL/dalpha through that dot product).  Same sums, re-associated; thresholds, alpha and the
-// T = T/(1-alpha) chain are untouched.
+//  1. Per pair a lane produces only TWO numbers: w = G * dL/dalpha and aT = alpha * T.  Everything the ten partial
+//     gradients need beyond those is a per-PIXEL constant:
+//        dL/dcolour_c, dL/ddepth   = sum_pix aT * (dL/dpixel_c | dL/ddepth_pix)
+//        dL/dopacity, dL/dmean2D, dL/dconic  follow from the six moments  sum_pix w * {1, x, y, x^2, xy, y^2}
+//     with (x, y) the pixel's position relative to the tile centre; the moments about the Gaussian's centre that the
+//     reference's formulas use (backward.cu:582-598) are recovered from them once per (tile, Gaussian) when the batch is
+//     flushed (dx = X - x with X the centre's offset from the tile centre: plain polynomial expansion).
+//  2. So the sum over a warp's 32 pixels for 8 Gaussians at a time is a small matrix product
+//        C[16 x 8] = A[16 x 64] * B[64 x 8],   A = per-pixel constants (6 monomial rows, 4 upstream-gradient rows),
+//                                              B = the (w | aT) values of 32 pixels x 8 Gaussians,
+//     which the warp runs on the tensor cores (mma.sync m16n8k8, TF32 inputs, FP32 accumulate) instead of a
+//     shuffle tree: lanes park (w, aT) of each visited Gaussian in a per-warp shared-memory panel (two STS per visit),
+//     and every 8 visits 20 HMMA instructions produce all ten sums of all eight Gaussians.  FP32 accuracy is kept by
+//     splitting the FP32 operands into TF32 high and low parts (x = hi + lo, products hi*hi + hi*lo + lo*hi; the
+//     monomials are small integers and exact): relative error ~2^-21 per term, far inside the 1e-4 gradient bar.
+//     r01 used a 12-shuffle / 22-select transpose-reduce per visit (~55 of 118 instructions per visit; ncu showed the
+//     ALU pipe, not FMA, as the busiest); this form needs ~16.
+//  3. The 8 warps of the tile add their 16x8 results into one per-batch shared-memory accumulator row per Gaussian
+//     (shared-memory atomics: 4 per lane per 8 visits), which the flush converts and sends to HBM as three
+//     red.global.add.v4.f32 per (tile, Gaussian).
+//
+// Per-pixel arithmetic follows the reference (same thresholds, same alpha, same T = T/(1-alpha) recurrence); only
+// the summation order / association of the gradient sums differs.  The 8x4 reach masks of blend_common.cuh skip
+// Gaussians that cannot touch a warp's pixels, and whole batches behind the tile's last contributor.
 //
 // Accumulator layout gacc[P][12] (zeroed by the caller):
 //   [0..3] dL/dmean2D.x, .y, dL/dopacity, dL/ddepth   [4..6] dL/dconic x,y,w
@@ -32,61 +37,117 @@
 
 namespace htgs {
 
-constexpr int BWD_BATCH = 128;  // 96 / 112 / 64 per batch and 5-6 CTAs per SM (48 / 40 registers) all measured slower
-constexpr int BWD_NV = 10;
+constexpr int BWD_BATCH = 128;   // staged Gaussians per batch (96 / 112 / 64 measured slower in r01)
+constexpr int PH_N = 8;          // Gaussians per tensor-core phase (the N of m16n8k8)
+constexpr int PH_STRIDE = 36;    // floats per panel row: 32 pixels + 4 pad => conflict-free STS.32 by lane and LDS.128 by fragment
+constexpr int ACC_STRIDE = 12;   // per-Gaussian tile sums: [0..5] moments 1,x,y,xx,xy,yy  [6..9] colour r,g,b + depth  [10..11] pad
 
-// value order inside the kernel: 0 w 1 w*dx 2 w*dy 3 depth-grad 4..6 w*dx*dx, w*dx*dy, w*dy*dy 7..9 rgb-grad
-struct Reduce10 {
-    bool b4, b3, b2, b1, writer;
-    int id;
-    __device__ __forceinline__ void init(int lane) {
-        b4 = lane & 16; b3 = lane & 8; b2 = lane & 4; b1 = lane & 2;
-        id = (b4 ? 5 : 0) + (b3 ? 3 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
-        const bool valid = b3 ? !b2 : !(b2 && b1);
-        writer = valid && !(lane & 1);
-    }
-    // returns, on writer lanes, the sum over the warp of v[id]
-    __device__ __forceinline__ float run(const float (&v)[BWD_NV]) const {
-        const unsigned full = 0xffffffffu;
-        float a[5], c[3], d[2];
-        float ak[5], ar[5];
-#pragma unroll
-        for (int k = 0; k < 5; k++) {
-            const float send = b4 ? v[k] : v[5 + k];
-            ak[k] = b4 ? v[5 + k] : v[k];
-            ar[k] = __shfl_xor_sync(full, send, 16);
-        }
-        up2(add2(pk2(ak[0], ak[1]), pk2(ar[0], ar[1])), a[0], a[1]);  // packed adds: one issue slot per pair
-        up2(add2(pk2(ak[2], ak[3]), pk2(ar[2], ar[3])), a[2], a[3]);
-        a[4] = ak[4] + ar[4];
-        float ck[3], cr[3];
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-            const float hi = (3 + k < 5) ? a[(3 + k < 5) ? 3 + k : 0] : 0.f;
-            const float send = b3 ? a[k] : hi;
-            ck[k] = b3 ? hi : a[k];
-            cr[k] = __shfl_xor_sync(full, send, 8);
-        }
-        up2(add2(pk2(ck[0], ck[1]), pk2(cr[0], cr[1])), c[0], c[1]);
-        c[2] = ck[2] + cr[2];
-        float dk[2], dr[2];
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-            const float hi = (k == 0) ? c[2] : 0.f;
-            const float send = b2 ? c[k] : hi;
-            dk[k] = b2 ? hi : c[k];
-            dr[k] = __shfl_xor_sync(full, send, 4);
-        }
-        up2(add2(pk2(dk[0], dk[1]), pk2(dr[0], dr[1])), d[0], d[1]);
-        const float send = b1 ? d[0] : d[1];
-        const float keep = b1 ? d[1] : d[0];
-        float e = keep + __shfl_xor_sync(full, send, 2);
-        e += __shfl_xor_sync(full, e, 1);
-        return e;
-    }
+// Per-warp shared memory of the reduction.
+//   park[r][lane]   r = 0..7: w of visit r, r = 8..15: aT of visit r - 8; column = lane = pixel index inside the warp's
+//                   8x4 block (y * 8 + x).  Rows are PH_STRIDE floats apart: STS.32 by lane and LDS.128 by fragment
+//                   lane are both bank-conflict free.
+//   afrag[ks][l]    the A operand (per-pixel constants), stored in FRAGMENT order: one float4 per (k-step, fragment lane
+//                   l = g*4 + t) = (A[g][k0], A[g+8][k0], A[g][k1], A[g+8][k1]) for the two pixels k0 = t*8 + 2ks,
+//                   k1 = k0 + 1 the lane covers in that k-step, so a single LDS.128 lands in the four consecutive
+//                   registers HMMA wants.  Rows of A:
+//                     0..5   monomials 1, x, y, xx, xy, yy of the pixel's tile position (small integers, exact in TF32)
+//                     6, 7   zero
+//                     8..11  TF32 high parts of dL/dpixel r, g, b and dL/ddepth
+//                     12..15 the low parts (d - hi) of the same four
+//                   With B = w the rows 0..5 give the six moments (rows 8..15 are ignored); with B = aT rows 8..11 +
+//                   rows 12..15 give the colour / depth sums (rows 0..7 are ignored).
+//   slot[v]         batch index of the Gaussian behind visit v of the open phase
+constexpr int PH_ROW_AT = 8, PH_PARK_ROWS = 16, PH_KSTEPS = 4;
+struct __align__(16) WarpPhase {
+    float park[PH_PARK_ROWS][PH_STRIDE];   // 2304 B
+    float4 afrag[PH_KSTEPS][32];           // 2048 B
+    uint32_t slot[PH_N];
 };
+constexpr uint32_t PH_OFF_AFRAG = PH_PARK_ROWS * PH_STRIDE * 4, PH_OFF_SLOT = PH_OFF_AFRAG + PH_KSTEPS * 32 * 16;
 
-// 4 CTAs per SM (64 registers): measured 1.12 ms against 1.27 ms at 3 CTAs (80 registers, 4 instructions fewer per visit)
+__device__ __forceinline__ void sts32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts32u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+// D += A * B, m16n8k8, A row-major 16x8 (a0: row g, col t | a1: row g+8, col t | a2: row g, col t+4 | a3: row g+8, col t+4),
+// B 8x8 (b0: row t, col g | b1: row t+4, col g), D 16x8 (d0,d1: row g, cols 2t,2t+1 | d2,d3: row g+8), g = lane>>2, t = lane&3.
+__device__ __forceinline__ void mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// first MMA of a chain: D = A * B (zero accumulator input, no register initialisation)
+__device__ __forceinline__ void mma_tf32_first(float (&d)[4], const float4& a, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                 : "r"(__float_as_uint(a.x)), "r"(__float_as_uint(a.y)), "r"(__float_as_uint(a.z)), "r"(__float_as_uint(a.w)),
+                   "r"(b0), "r"(b1), "f"(0.f));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const float4& a, uint32_t b0, uint32_t b1) {
+    mma_tf32(d, __float_as_uint(a.x), __float_as_uint(a.y), __float_as_uint(a.z), __float_as_uint(a.w), b0, b1);
+}
+// x = hi + lo exactly: hi = x rounded to nearest TF32 (13 low mantissa bits clear), so |lo| <= 2^-12 |x| and what the
+// tensor core drops of lo is below 2^-23 |x|
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
+
+// One tensor-core phase of a warp: sums the parked (w, aT) of `cnt` <= 8 visits over the warp's 32 pixels against the
+// per-pixel constants and adds the 10 x cnt results into the batch accumulator rows.  ph = shared address of the
+// warp's WarpPhase, acc = shared address of s_acc.  Warp-collective (all 32 lanes, converged).
+__device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, int cnt, int lane) {
+    __syncwarp();
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t aw = ph + (uint32_t)g * (PH_STRIDE * 4u) + (uint32_t)t * 32u;   // visit g, pixels t*8 .. t*8+7
+    const uint32_t aa = aw + (uint32_t)PH_ROW_AT * (PH_STRIDE * 4u);
+    const uint32_t af = ph + PH_OFF_AFRAG + (uint32_t)lane * 16u;
+    float cw1[4], cw2[4], ca1[4], ca2[4];  // four independent chains: (w_hi, w_lo, aT_hi, aT_lo) against the same A
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const float4 w4 = lds128(aw + half * 16), t4 = lds128(aa + half * 16);
+        const float wv[4] = {w4.x, w4.y, w4.z, w4.w}, tv[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+        for (int k = 0; k < 2; k++) {  // k-step 2*half + k: elements 2k (k-index t) and 2k+1 (k-index t+4)
+            const float4 a = lds128(af + (uint32_t)(2 * half + k) * (32u * 16u));
+            uint32_t wh0, wl0, wh1, wl1, th0, tl0, th1, tl1;
+            split_tf32(wv[2 * k], wh0, wl0);
+            split_tf32(wv[2 * k + 1], wh1, wl1);
+            split_tf32(tv[2 * k], th0, tl0);
+            split_tf32(tv[2 * k + 1], th1, tl1);
+            if (half == 0 && k == 0) {
+                mma_tf32_first(cw1, a, wh0, wh1);
+                mma_tf32_first(cw2, a, wl0, wl1);
+                mma_tf32_first(ca1, a, th0, th1);
+                mma_tf32_first(ca2, a, tl0, tl1);
+            } else {
+                mma_tf32(cw1, a, wh0, wh1);
+                mma_tf32(cw2, a, wl0, wl1);
+                mma_tf32(ca1, a, th0, th1);
+                mma_tf32(ca2, a, tl0, tl1);
+            }
+        }
+    }
+    // lane (g, t) holds rows g and g+8 of columns (visits) 2t and 2t+1
+    const float x0 = cw1[0] + cw2[0], x1 = cw1[1] + cw2[1];   // moment g            (g < 6)
+    float y0 = ca1[2] + ca2[2], y1 = ca1[3] + ca2[3];         // colour/depth row g+8: high-part rows for g < 4, low-part rows above
+    y0 += __shfl_xor_sync(0xffffffffu, y0, 16);               // lane g+4 holds the low-part row of the same quantity
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 16);
+    uint32_t s0, s1;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(s0), "=r"(s1) : "r"(ph + PH_OFF_SLOT + (uint32_t)t * 8u) : "memory");
+    const bool v0 = 2 * t < cnt, v1 = 2 * t + 1 < cnt;
+    float* accp = reinterpret_cast<float*>(__cvta_shared_to_generic((size_t)acc));
+    if (g < 6) {
+        if (v0 && x0 != 0.f) atomicAdd(accp + s0 * ACC_STRIDE + g, x0);
+        if (v1 && x1 != 0.f) atomicAdd(accp + s1 * ACC_STRIDE + g, x1);
+    }
+    if (g < 4) {
+        if (v0 && y0 != 0.f) atomicAdd(accp + s0 * ACC_STRIDE + 6 + g, y0);
+        if (v1 && y1 != 0.f) atomicAdd(accp + s1 * ACC_STRIDE + 6 + g, y1);
+    }
+    __syncwarp();
+}
+
+// 4 CTAs per SM (64 registers; r01: 1.12 ms at 4 CTAs against 1.27 ms at 3); shared memory 46.9 KB per CTA
 constexpr int BWD_MIN_BLOCKS = 4;
 __global__ void __launch_bounds__(HTGS_TILE_PIX, BWD_MIN_BLOCKS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -95,16 +156,17 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       const float* __restrict__ alphas, const uint32_t* __restrict__ n_contrib,
                       const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth_pix,
                       const float* __restrict__ dL_dalpha_pix, float* __restrict__ gacc) {
-    __shared__ float s_stage[BLEND_WARPS][BWD_BATCH][BWD_NV];  // 40 KB
-    __shared__ StagedGaussian s_g[BWD_BATCH];
+    __shared__ WarpPhase s_ph[BLEND_WARPS];                          // 35 072 B
+    __shared__ __align__(16) float s_acc[BWD_BATCH][ACC_STRIDE];     //  6 144 B
+    __shared__ StagedGaussian s_g[BWD_BATCH];                        //  6 144 B
     __shared__ uint32_t s_id[BWD_BATCH];
     __shared__ uint8_t s_mask[BWD_BATCH];
     __shared__ uint32_t s_warp_last[BLEND_WARPS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile_x0 = blockIdx.x * HTGS_TILE, tile_y0 = blockIdx.y * HTGS_TILE;
-    const int px = tile_x0 + warp_block_x(warp) + (lane & 7);
-    const int py = tile_y0 + warp_block_y(warp) + (lane >> 3);
+    const int lx = warp_block_x(warp) + (lane & 7), ly = warp_block_y(warp) + (lane >> 3);  // position inside the tile
+    const int px = tile_x0 + lx, py = tile_y0 + ly;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     const size_t pix = (size_t)py * W + px;
@@ -122,8 +184,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         d0 = dL_dpix[pix];
         d1 = dL_dpix[plane + pix];
         d2 = dL_dpix[2 * plane + pix];
-        dd = dL_ddepth_pix[pix];
-        da = dL_dalpha_pix[pix];
+        if (dL_ddepth_pix) dd = dL_ddepth_pix[pix];   // NULL = no upstream gradient for that output (importance pass)
+        if (dL_dalpha_pix) da = dL_dalpha_pix[pix];
     }
     // -(T_final * bg . dL/dpixel): numerator of the background term, backward.cu:575-578
     const float bg_k = -T_final * (bg[0] * d0 + bg[1] * d1 + bg[2] * d2);
@@ -131,6 +193,33 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     // A = sum_ch accum_rec[ch]*dL/dch (colour, depth, alpha channels); Cprev = the same dot product
     // for the previously visited Gaussian's own colour/depth/1
     float A = 0.f, Cprev = 0.f, last_alpha = 0.f, one_m_last = 1.f;  // one_m_last = 1 - last_alpha, carried instead of recomputed
+
+    // This pixel's column of the A operand, scattered into fragment order: pixel p = lane sits in k-step (p & 7) >> 1,
+    // fragment lanes g*4 + (p >> 3) for every row pair (g, g+8), element (p & 1) of the k-step's pixel pair.
+    const uint32_t ph = smem_u32(&s_ph[warp]);
+    {
+        // pixel position relative to the tile CENTRE (half-integers in [-7.5, 7.5]; squares <= 56.25: exact in TF32).
+        // Centring keeps the offset X of a Gaussian that matters to this tile small, which bounds the cancellation in
+        // the moment shift of the flush (X^2 S0 - 2 X Sx + Sxx) by ~(X / sigma)^2 <= a few hundred.
+        const float fx = (float)lx - 7.5f, fy = (float)ly - 7.5f;
+        const float lo_row[8] = {1.f, fx, fy, fx * fx, fx * fy, fy * fy, 0.f, 0.f};  // A rows 0..7
+        float hi_row[8];                                                               // A rows 8..15
+        const float dv[4] = {d0, d1, d2, dd};
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            uint32_t hi, lo;
+            split_tf32(dv[r], hi, lo);
+            hi_row[r] = __uint_as_float(hi);
+            hi_row[4 + r] = __uint_as_float(lo);
+        }
+        const uint32_t e = ph + PH_OFF_AFRAG + (uint32_t)((lane & 7) >> 1) * (32u * 16u) + (uint32_t)(lane >> 3) * 16u +
+                           (uint32_t)(lane & 1) * 8u;
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+            sts32(e + (uint32_t)g * 64u, lo_row[g]);       // .x / .z of fragment lane g*4 + t
+            sts32(e + (uint32_t)g * 64u + 4u, hi_row[g]);  // .y / .w
+        }
+    }
 
     uint32_t wl = last_contributor;
 #pragma unroll
@@ -143,10 +232,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     for (int w = 0; w < BLEND_WARPS; w++) block_last = max(block_last, s_warp_last[w]);
 
     const uint64_t pxy = pk2(pxf, pyf), d0_d1 = pk2(d0, d1), d2_dd = pk2(d2, dd), da_0 = pk2(da, 0.f);
-    Reduce10 red;
-    red.init(lane);
     const uint32_t sg_base = smem_u32(s_g);
-    const uint32_t stage_base = smem_u32(&s_stage[warp][0][0]) + (uint32_t)red.id * 4u;
+    const uint32_t acc_base = smem_u32(s_acc);
+    const uint32_t park = ph + (uint32_t)lane * 4u;                          // this lane's column of the (w | aT) panel
+    const uint32_t slot_base = ph + PH_OFF_SLOT;
 
     for (int base = 0; base < n; base += BWD_BATCH) {
         const int cnt = min(BWD_BATCH, n - base);
@@ -161,14 +250,17 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             s_id[tid] = g;
             stage_gaussian(&s_g[tid], xy, co, feat[g]);
             s_mask[tid] = (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
+            float4* a4 = reinterpret_cast<float4*>(&s_acc[tid][0]);
+            a4[0] = a4[1] = a4[2] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         __syncthreads();
+        int parked = 0;           // visits parked in the warp's panel since its last tensor-core phase (warp-uniform)
+        uint32_t park_at = park;  // where this lane parks the next visit; the slot word sits at a fixed distance pattern
         for (int c0 = 0; c0 < cnt; c0 += 32) {
             const int j = c0 + lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1) && (uint32_t)(top - j) < warp_last;
             uint32_t m = __ballot_sync(0xffffffffu, mine);
             const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
-            const uint32_t chunk_stage = stage_base + (uint32_t)c0 * (BWD_NV * 4u);
             const uint32_t chunk_top = (uint32_t)(top - c0);
             while (m) {
                 const int b = __ffs(m) - 1;
@@ -186,9 +278,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const float alpha = fminf(0.99f, MU(q1.y, G));
                 // `contributor` after its decrement is chunk_top - b (backward.cu:517-519)
                 const bool live = (chunk_top - (uint32_t)b) < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                // Everything a lane contributes is proportional to w = G*dL/dalpha or to aT = alpha*T: lanes that do
-                // not blend this Gaussian carry w = aT = 0 and the ten products are formed once, outside the branch
-                // (zeroing two scalars instead of ten values).
+                // Everything a lane contributes is proportional to w = G*dL/dalpha or to aT = alpha*T; lanes that do
+                // not blend this Gaussian park zeros.
                 float w = 0.f, aT = 0.f;
                 if (live) {
                     const float2 q2 = lds64(a + 32);  // b, depth
@@ -212,52 +303,45 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
                     w = G * dL_dopa;
                 }
-                float total = 0.f;
                 if (__any_sync(0xffffffffu, live)) {
-                    float v[BWD_NV];
-                    const uint64_t wd = mul2(pk2(w, w), dxy);  // (w*dx, w*dy)
-                    float wdx, wdy;
-                    up2(wd, wdx, wdy);
-                    v[0] = w;          // -> dL/dopacity, and scaled by opacity the common factor below
-                    v[1] = wdx;        // first moments  -> dL/dmean2D
-                    v[2] = wdy;
-                    up2(mul2(wd, dxy), v[4], v[6]);  // second moments w*dx*dx, w*dy*dy -> dL/dconic
-                    v[5] = wdx * dy;
-                    const uint64_t aTaT = pk2(aT, aT);
-                    up2(mul2(aTaT, d0_d1), v[7], v[8]);  // dL/dcolour r, g
-                    up2(mul2(aTaT, d2_dd), v[9], v[3]);  // dL/dcolour b, dL/ddepth
-                    total = red.run(v);
+                    sts32(park_at, w);
+                    sts32(park_at + (uint32_t)(PH_ROW_AT * PH_STRIDE * 4), aT);
+                    sts32u(slot_base + (uint32_t)parked * 4u, (uint32_t)(c0 + b));  // same value from every lane
+                    park_at += (uint32_t)(PH_STRIDE * 4);
+                    if (++parked == PH_N) {
+                        reduce_phase(ph, acc_base, PH_N, lane);
+                        parked = 0;
+                        park_at = park;
+                    }
                 }
-                if (red.writer)
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(chunk_stage + (uint32_t)b * (BWD_NV * 4u)), "f"(total) : "memory");
             }
         }
+        if (parked) reduce_phase(ph, acc_base, parked, lane);
         __syncthreads();
         if (tid < cnt) {
-            float s[BWD_NV];
-#pragma unroll
-            for (int k = 0; k < BWD_NV; k++) s[k] = 0.f;
-            const uint32_t mask = s_mask[tid];
-            const uint32_t pos0 = (uint32_t)(top - tid);
-#pragma unroll
-            for (int w = 0; w < BLEND_WARPS; w++) {
-                if (((mask >> w) & 1) && pos0 < s_warp_last[w]) {
-#pragma unroll
-                    for (int k = 0; k < BWD_NV; k++) s[k] += s_stage[w][tid][k];
-                }
-            }
-            // moments -> gradients (backward.cu:582-598), per-Gaussian constants applied once here
+            const float4* a4 = reinterpret_cast<const float4*>(&s_acc[tid][0]);
+            const float4 m0 = a4[0], m1 = a4[1], m2 = a4[2];
+            const float S0 = m0.x, Sx = m0.y, Sy = m0.z, Sxx = m0.w, Sxy = m1.x, Syy = m1.y;
+            const float gr = m1.z, gg = m1.w, gb = m2.x, gdepth = m2.y;
             const float4 q0 = s_g[tid].q0;
             const float4 q1 = s_g[tid].q1;
+            // moments about the Gaussian's centre from the moments about the tile centre: d = (X - x, Y - y)
+            const float X = q0.x - ((float)tile_x0 + 7.5f), Y = q0.y - ((float)tile_y0 + 7.5f);
+            const float s1 = fmaf(X, S0, -Sx), s2 = fmaf(Y, S0, -Sy);           // sum w dx, sum w dy
+            const float s4 = fmaf(X, s1 - Sx, Sxx);                             // sum w dx dx
+            const float s5 = fmaf(X, s2, fmaf(-Y, Sx, Sxy));                    // sum w dx dy
+            const float s6 = fmaf(Y, s2 - Sy, Syy);                             // sum w dy dy
+            // moments -> gradients (backward.cu:582-598), per-Gaussian constants applied once here
             const float cx = q0.z, cz = q0.w, cy = q1.x, op = q1.y;
             const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:490-491
-            const float gmx = -op * (cx * s[1] + cy * s[2]) * ddelx_dx;
-            const float gmy = -op * (cz * s[2] + cy * s[1]) * ddely_dy;
-            const float gcx = -0.5f * op * s[4], gcy = -0.5f * op * s[5], gcw = -0.5f * op * s[6];
+            const float gmx = -op * (cx * s1 + cy * s2) * ddelx_dx;
+            const float gmy = -op * (cz * s2 + cy * s1) * ddely_dy;
+            const float gcx = -0.5f * op * s4, gcy = -0.5f * op * s5, gcw = -0.5f * op * s6;
             float4* dst = reinterpret_cast<float4*>(gacc + (size_t)s_id[tid] * 12);
-            if (s[0] != 0.f || s[1] != 0.f || s[2] != 0.f || s[3] != 0.f) atomicAdd(dst, make_float4(gmx, gmy, s[0], s[3]));
-            if (s[4] != 0.f || s[5] != 0.f || s[6] != 0.f) atomicAdd(dst + 1, make_float4(gcx, gcy, gcw, 0.f));
-            if (s[7] != 0.f || s[8] != 0.f || s[9] != 0.f) atomicAdd(dst + 2, make_float4(s[7], s[8], s[9], 0.f));
+            if (S0 != 0.f || Sx != 0.f || Sy != 0.f || gdepth != 0.f) atomicAdd(dst, make_float4(gmx, gmy, S0, gdepth));
+            if (S0 != 0.f || Sx != 0.f || Sy != 0.f || Sxx != 0.f || Sxy != 0.f || Syy != 0.f)
+                atomicAdd(dst + 1, make_float4(gcx, gcy, gcw, 0.f));
+            if (gr != 0.f || gg != 0.f || gb != 0.f) atomicAdd(dst + 2, make_float4(gr, gg, gb, 0.f));
         }
     }
 }

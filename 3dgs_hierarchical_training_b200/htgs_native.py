@@ -64,6 +64,12 @@ _SIGNATURES = {
     "htgs_allreduce_p2p": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, ctypes.c_longlong, c_void_p]),
     "htgs_allreduce_multimem": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p]),
     "htgs_allreduce_set_launch_shape": (c_int, [c_int, c_int]),
+    # (P, D, M, R, W, H, bg, means3D, campos, alphas, radii, geom, binning, image, dL_dcolor, scratch, importance, stream)
+    "htgs_importance_accumulate": (c_int, [c_int, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "htgs_importance_select_workspace_bytes": (c_size_t, [c_int]),
+    "htgs_importance_select": (c_int, [c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "htgs_transform_points": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_row_scan_scratch_bytes": (c_size_t, [c_int]),
     "htgs_row_scan": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "htgs_rows_compact": (c_int, [c_int, c_void_p, c_void_p, c_int, ctypes.POINTER(RowTensor), c_void_p]),

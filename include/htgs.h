@@ -277,6 +277,29 @@ int htgs_rows_append(int P, const uint8_t* mask, const void* scratch, int n_tens
 int htgs_rows_split(int P, int N, uint32_t count, const uint8_t* mask, const void* scratch, int n_tensors,
                     const htgs_row_tensor* tensors, void* stream);
 
+/* ---- merge-time operations of the hierarchical trainer (second half; opt-in) ----
+ * htgs_importance_accumulate  one view of calc_importance (trainer/ht3dgs_trainer.py:1428-1462): for loss = image.sum()
+ *     (dL_dout_color = that loss's gradient with respect to the rendered colour, [3,H,W]; depth and alpha receive none)
+ *     importance[i][k][c] += |dL/dsh[i][k][c]|, importance float32 [P, M, 3] kept by the caller across the views of a
+ *     segment (zero it first; divide by the pixel count afterwards as the reference does).  Runs the blend backward of
+ *     the LAST forward (same geometry / binning / image buffers and alphas as htgs_backward) and forms the outer product
+ *     of the SH basis with the clamp-masked colour gradient directly: no geometry backward, no gradient tensors, none of
+ *     the reference's three abs() hooks.  scratch from htgs_backward_scratch_bytes(P).
+ * htgs_importance_select      the bottom-k choice of merge_two_3DGS (:232-238, :246-251): mask[i] = 1 for the k Gaussians
+ *     with the smallest max_j importance[i][j] (n_per values per Gaussian), 0 elsewhere.  Ties are broken towards
+ *     the lower index (stable radix sort of (amax bits, index) with this library's own sort; torch.topk leaves the
+ *     choice among equal values unspecified).  workspace from htgs_importance_select_workspace_bytes(P), 256-B aligned.
+ * htgs_transform_points       out[i] = (T [x_i 1])[:3] / (T [x_i 1])[3] for a row-major 4x4 T in DEVICE memory: the
+ *     source model's positions carried into the destination frame (:254-257). */
+int htgs_importance_accumulate(int P, int D, int M, int64_t R, int W, int H, const float* background,
+                               const float* means3D, const float* campos, const float* alphas, const int* radii,
+                               const void* geom_buf, const void* binning_buf, const void* image_buf,
+                               const float* dL_dout_color, void* scratch, float* importance, void* stream);
+size_t htgs_importance_select_workspace_bytes(int P);
+int htgs_importance_select(int P, int n_per, const float* importance, int64_t k, void* workspace, uint8_t* mask,
+                           void* stream);
+int htgs_transform_points(int P, const float* xyz, const float* transform, float* out, void* stream);
+
 /* ---- un-activated, un-concatenated parameters (opt-in) ----
  * The HT model stores _scaling, _rotation, _opacity, _features_dc [P,1,3] and _features_rest [P,15,3]
  * and every render call first materialises exp / F.normalize / sigmoid / torch.cat of them
