@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libhtgs.so")
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "radix_sort.cu", "blend_forward.cu", "blend_backward.cu",
-           "geom_backward.cu", "knn.cu", "sort_static.cu", "train_tail.cu", "loss_l1_ssim.cu", "densify.cu", "allreduce_p2p.cu", "merge_ops.cu"]
+           "geom_backward.cu", "knn.cu", "sort_static.cu", "train_tail.cu", "loss_l1_ssim.cu", "densify.cu", "allreduce_p2p.cu", "merge_ops.cu", "sh_compact.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"]
 

@@ -307,6 +307,7 @@ int htgs_forward_render_capacity(int P, int64_t capacity, int W, int H, const fl
 }
 
 static int backward_impl(const char* who, const float* shs_rest, const float* opacity_raw, float* dL_dsh_rest,
+                         float* rgb_slot, bool rgb_multicast,
                          int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
                   const float* shs, const float* colors_precomp, const float* alphas, const float* scales,
                   float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
@@ -323,7 +324,8 @@ static int backward_impl(const char* who, const float* shs_rest, const float* op
         set_error("%s: null required pointer", who);
         return 1;
     }
-    if (shs && !dL_dsh) { set_error("%s: dL_dsh required with shs", who); return 1; }
+    if (shs && !dL_dsh && !rgb_slot) { set_error("%s: dL_dsh required with shs", who); return 1; }
+    if (rgb_slot && (!shs || (reinterpret_cast<size_t>(rgb_slot) & 15))) { set_error("%s: the colour-gradient slot needs the SH path and 16-byte alignment", who); return 1; }
     if (colors_precomp && !dL_dcolors) { set_error("%s: dL_dcolors required with colors_precomp", who); return 1; }
     if (scales && (!rotations || !dL_dscales || !dL_drotations)) { set_error("%s: scale/rotation outputs required", who); return 1; }
     if (!scales && !cov3D_precomp) { set_error("%s: need scales+rotations or cov3D_precomp", who); return 1; }
@@ -344,6 +346,8 @@ static int backward_impl(const char* who, const float* shs_rest, const float* op
         if (launch_blend_backward(P, W, H, img.ranges, b.values_sorted, g, background, alphas, img.n_contrib, dL_dout_color,
                                   dL_dout_depth, dL_dout_alpha, gacc, st)) return 1;
     }
+    // compact SH mode: the clamp-masked colour gradient leaves for its view slot as soon as the blend backward is done
+    if (rgb_slot && launch_rgb_extract(P, gacc, g.clamped, campos, rgb_slot, rgb_multicast, st)) return 1;
     // the SH path feeds dL/dcolour into dL/dsh; only the precomputed-colour path returns it
     StageTimer t(ST_GEOM_BWD, st);
     if (launch_geom_backward(P, D, M, means3D, radii, shs, shs_rest, opacity_raw, dL_dsh_rest, colors_precomp, scales, scale_modifier, rotations, cov3D_precomp,
@@ -360,10 +364,26 @@ int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* bac
                   const float* dL_dout_depth, const float* dL_dout_alpha, void* scratch, float* dL_dmeans2D,
                   float* dL_dopacity, float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                   float* dL_dscales, float* dL_drotations, void* stream) {
-    return backward_impl("htgs_backward", nullptr, nullptr, nullptr, P, D, M, R, W, H, background, means3D, shs, colors_precomp,
+    return backward_impl("htgs_backward", nullptr, nullptr, nullptr, nullptr, false, P, D, M, R, W, H, background, means3D, shs, colors_precomp,
                          alphas, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx,
                          tanfovy, radii, geom_buf, binning_buf, image_buf, dL_dout_color, dL_dout_depth, dL_dout_alpha, scratch,
                          dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, stream);
+}
+
+int htgs_backward_compact(int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
+                          const float* shs, const float* alphas, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                          const float* campos, float tanfovx, float tanfovy, const int* radii, const void* geom_buf,
+                          const void* binning_buf, const void* image_buf, const float* dL_dout_color, const float* dL_dout_depth,
+                          const float* dL_dout_alpha, void* scratch, float* dL_dmeans2D, float* dL_dopacity, float* dL_dmeans3D,
+                          float* dL_dcov3D, float* dL_dscales, float* dL_drotations, float* rgb_slot, int rgb_slot_is_multicast,
+                          void* stream) {
+    if (P > 0 && (!shs || !rgb_slot)) { set_error("htgs_backward_compact: shs and rgb_slot are required"); return 1; }
+    return backward_impl("htgs_backward_compact", nullptr, nullptr, nullptr, rgb_slot, rgb_slot_is_multicast != 0, P, D, M, R, W, H,
+                         background, means3D, shs, nullptr, alphas, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
+                         projmatrix, campos, tanfovx, tanfovy, radii, geom_buf, binning_buf, image_buf, dL_dout_color,
+                         dL_dout_depth, dL_dout_alpha, scratch, dL_dmeans2D, dL_dopacity, nullptr, dL_dmeans3D, dL_dcov3D, nullptr,
+                         dL_dscales, dL_drotations, stream);
 }
 
 int htgs_backward_raw(int P, int D, int64_t R, int W, int H, const float* background, const float* xyz,
@@ -385,7 +405,7 @@ int htgs_backward_raw(int P, int D, int64_t R, int W, int H, const float* backgr
         set_error("%s: features_rest and its gradient must be 16-byte aligned", who);
         return 1;
     }
-    return backward_impl(who, features_rest, opacity_raw, dL_dfeatures_rest, P, D, 16, R, W, H, background, xyz, features_dc,
+    return backward_impl(who, features_rest, opacity_raw, dL_dfeatures_rest, nullptr, false, P, D, 16, R, W, H, background, xyz, features_dc,
                          nullptr, alphas, scaling_raw, scale_modifier, rotation_raw, nullptr, viewmatrix, projmatrix, campos,
                          tanfovx, tanfovy, radii, geom_buf, binning_buf, image_buf, dL_dout_color, dL_dout_depth, dL_dout_alpha,
                          scratch, dL_dmeans2D, dL_dopacity_raw, nullptr, dL_dxyz, nullptr, dL_dfeatures_dc, dL_dscaling_raw,

@@ -89,6 +89,9 @@ int launch_geom_backward(int P, int D, int M, const float* means3D, const int* r
                          float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
                          float* dL_drotations, cudaStream_t st);
 
+int launch_rgb_extract(int P, const float* gacc, const uint8_t* clamped, const float* campos, float* slot, bool multicast,
+                       cudaStream_t st);
+
 size_t sort_scratch_bytes(int64_t n);
 int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t* k_out, uint32_t* v_out,
                void* scratch, cudaStream_t st, const uint32_t* n_dev = nullptr);

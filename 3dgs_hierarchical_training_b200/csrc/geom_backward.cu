@@ -296,6 +296,9 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
                 e[k] = w[1 + k / 3] * (c == 0 ? r0 : (c == 1 ? r1 : r2));
             }
             store_rest_row(dL_dsh_rest, idx, e);
+        } else if (dL_dsh == nullptr) {
+            // compact SH mode (htgs_backward_compact): the expanded 192 B/Gaussian gradient is not written here at all; the
+            // clamp-masked colour gradient it is the outer product of has already left through rgb_extract_kernel
         } else if (fast && sh_vec) {
             // twelve 128-bit stores; coefficient and channel of every element are compile-time
 #pragma unroll

@@ -60,9 +60,25 @@ def _arena_or_empty(name, shape, **opts):
         if rng is not None and rng[1] - rng[0] == n and flat.device == opts["device"]:
             owner = owners.get(name) if owners else None
             held = owner is not None and owner.grad is not None and owner.grad.data_ptr() == flat.data_ptr() + 4 * rng[0]
-            if not held:
+            # dL_drotations is written with 128-bit stores: a slice that does not start 16-byte aligned (P not a multiple
+            # of 4 in the flat 59-float layout) gets an ordinary tensor and is packed by the reducer afterwards
+            misaligned = name == "rotations" and (flat.data_ptr() + 4 * rng[0]) % 16 != 0
+            if not held and not misaligned:
                 return flat[rng[0]:rng[1]].view(shape)  # a fresh view object: autograd may adopt it as .grad
     return torch.empty(shape, **opts)
+
+
+# Optional compact SH mode (view-parallel training, htgs_dist.CompactSHGradReducer): when set, the backward of the SH
+# path does not produce dL_dsh at all.  It writes the clamp-masked colour gradient and the camera position of the view
+# into the slot the provider names (htgs_backward_compact) and returns None for the SH gradient; the reducer rebuilds
+# the summed dL_dsh from the slots of all views on every rank.
+_SH_COMPACT = None
+
+
+def set_sh_compact(provider):
+    """provider(device) -> (slot_ptr: int, is_multicast: bool) for the next backward on that device; None clears."""
+    global _SH_COMPACT
+    _SH_COMPACT = provider
 
 
 def _pinned_counter(dev):
@@ -192,10 +208,27 @@ def backward_impl(background, means3D, radii, colors, scales, rotations, scale_m
         want_cov = has_cov or mirror_all
         dcolors = torch.empty((P, NUM_CHANNELS), **f32) if want_colors else None
         dcov3D = torch.empty((P, 6), **f32) if want_cov else None
-        dsh = _arena_or_empty("shs", (P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
+        compact = _SH_COMPACT is not None and has_sh and not has_colors
+        if compact:
+            dsh = None
+        else:
+            dsh = _arena_or_empty("shs", (P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
         dscales = _arena_or_empty("scales", (P, 3), **f32) if has_scales else torch.zeros((P, 3), **f32)
         drot = _arena_or_empty("rotations", (P, 4), **f32) if has_scales else torch.zeros((P, 4), **f32)
         scratch = torch.empty(lib.htgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        if compact:
+            slot_ptr, slot_mc = _SH_COMPACT(dev)
+            nat.check(lib.htgs_backward_compact(
+                P, int(degree), M, int(R), W, H, nat.ptr(background), nat.ptr(means3D), nat.ptr(sh), nat.ptr(alphas),
+                nat.ptr(scales), float(scale_modifier), nat.ptr(rotations), nat.ptr(cov3D_precomp), nat.ptr(viewmatrix),
+                nat.ptr(projmatrix), nat.ptr(campos), float(tan_fovx), float(tan_fovy), radii.data_ptr(), geomBuffer.data_ptr(),
+                nat.ptr(binningBuffer), imageBuffer.data_ptr(), nat.ptr(dL_dout_color), nat.ptr(dL_dout_depth),
+                nat.ptr(dL_dout_alpha), scratch.data_ptr(), dmeans2D.data_ptr(), dopacity.data_ptr(), dmeans3D.data_ptr(),
+                nat.ptr(dcov3D), nat.ptr(dscales) if has_scales else None, nat.ptr(drot) if has_scales else None,
+                ctypes.c_void_p(int(slot_ptr)), int(bool(slot_mc)), st), "htgs_backward_compact")
+            if debug:
+                torch.cuda.synchronize(dev)
+            return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
         nat.check(lib.htgs_backward(
             P, int(degree), M, int(R), W, H, nat.ptr(background), nat.ptr(means3D), nat.ptr(sh), nat.ptr(colors),
             nat.ptr(alphas), nat.ptr(scales), float(scale_modifier), nat.ptr(rotations), nat.ptr(cov3D_precomp),

@@ -161,3 +161,160 @@ def reduce_densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_
     xyz_gradient_accum.add_(inc[0].view_as(xyz_gradient_accum))
     denom.add_(inc[1].view_as(denom))
     torch.maximum(max_radii2D, rad.view_as(max_radii2D), out=max_radii2D)
+
+
+# ---- compact SH exchange: ranks trade the colour gradient, not the expanded SH gradient ----
+# 11 floats/Gaussian are all-reduced; the 48 SH floats are rebuilt from 3 floats per view.  Rotations first: the kernels
+# write dL_drotations with 128-bit stores, so its slice must start 16-byte aligned for every P.
+SMALL_ORDER = ("rotations", "means3D", "opacities", "scales")
+SMALL_FLOATS = (4, 3, 1, 3)
+
+
+class CompactSHGradReducer:
+    """View-parallel gradient exchange that never ships dL_dsh (81 % of the flat 59-float gradient).
+
+    Per view, dL_dsh[i] is the outer product of the SH basis of Gaussian i's view direction with the clamp-masked colour
+    gradient r[i] (3 floats).  Each rank's backward writes r and the camera position of its views into view SLOTS
+    (diff_gaussian_rasterization/_C.py compact mode -> htgs_backward_compact); `all_reduce()` then
+      1. all-reduces the remaining 11 floats/Gaussian (xyz, opacity, scaling, rotation), and
+      2. rebuilds sum_views basis (x) r on every rank from ALL views' slots, in view order (htgs_sh_expand), so replicas
+         stay bit-identical,
+    moving 44 + 12 * views bytes per Gaussian instead of 236.  Transports for the slots:
+      peer_memory="multimem"  the backward pushes its slot through the NVSwitch multicast mapping into every rank's buffer;
+      peer_memory="p2p"       slots stay local, the rebuild reads the other ranks' slots with NVLink peer loads;
+      peer_memory=False       torch.distributed all_gather of the slots (NCCL; any backend).
+    `views_total` slots exist per step; rank r owns views [r * views_total / world, (r + 1) * views_total / world).
+    Usage per step: begin_step(); forward/backward of each local view (parameters' .grad for xyz/opacity/scaling/rotation
+    land in the small flat buffer through the gradient arena); all_reduce(D); grads(like) returns all five gradients."""
+
+    def __init__(self, P, device, views_total=None, peer_memory=False, M=16):
+        import ctypes
+        import htgs_native as nat
+        self.P, self.M, self.device = int(P), int(M), device
+        self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        self.rank = dist.get_rank() if self.world > 1 else 0
+        self.views_total = int(views_total) if views_total is not None else self.world
+        if self.views_total % self.world:
+            raise RuntimeError(f"{self.views_total} views do not divide over {self.world} ranks")
+        if self.views_total > 16:
+            raise RuntimeError("at most 16 view slots per step")
+        self.views_per_rank = self.views_total // self.world
+        self.slot_floats = int(nat.lib().htgs_sh_slot_floats(self.P))
+        n_small = 11 * self.P
+        self.n_small_pad = (n_small + 3) // 4 * 4
+        total = self.n_small_pad + self.views_total * self.slot_floats
+        self._peer = None
+        self.collective = "nccl"
+        if peer_memory and self.world > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            buf = symm_mem.empty(total, dtype=torch.float32, device=device)
+            hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
+            buf.zero_()
+            off = buf.data_ptr() - int(hdl.buffer_ptrs[hdl.rank])
+            ptrs = [int(p) + off for p in hdl.buffer_ptrs]
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            want_mc = peer_memory == "multimem" or (peer_memory is True and mc and hdl.world_size > 2)
+            if want_mc and not mc:
+                raise RuntimeError("multimem transport requested but the symmetric-memory handle has no multicast address")
+            self.collective = "multimem" if want_mc else "p2p"
+            self._peer = dict(buf=buf, hdl=hdl, ptrs=ptrs, table=(ctypes.c_void_p * hdl.world_size)(*ptrs), mc=(mc + off) if mc else 0)
+            self.buf = buf
+        else:
+            self.buf = torch.zeros(total, device=device, dtype=torch.float32)
+        self.flat = self.buf[:n_small]
+        self.slices = {}
+        o = 0
+        for name, per in zip(SMALL_ORDER, SMALL_FLOATS):
+            self.slices[name] = (o, o + self.P * per)
+            o += self.P * per
+        self.sh_grad = torch.zeros((self.P, self.M, 3), device=device, dtype=torch.float32)
+        self._next_local = 0
+
+    # -- slots --
+    def _slot_offset(self, view):
+        return self.n_small_pad + view * self.slot_floats
+
+    def slot(self, view):
+        o = self._slot_offset(view)
+        return self.buf[o:o + self.slot_floats]
+
+    def begin_step(self):
+        self._next_local = 0
+
+    def _provider(self, dev):
+        if self._next_local >= self.views_per_rank:
+            raise RuntimeError("more backward passes in this step than view slots owned by this rank; call begin_step()")
+        view = self.rank * self.views_per_rank + self._next_local
+        self._next_local += 1
+        off = 4 * self._slot_offset(view)
+        if self.collective == "multimem":
+            return self._peer["mc"] + off, True
+        return self.buf.data_ptr() + off, False
+
+    def install(self, params=None):
+        """Routes the rasterizer backward into this reducer: small gradients into the flat buffer (arena), colour
+        gradients into the view slots (compact SH mode)."""
+        from diff_gaussian_rasterization import _C
+        owners = {k: v for k, v in params.items() if k in SMALL_ORDER} if params else None
+        _C.set_grad_arena(self.flat, self.slices, owners)
+        _C.set_sh_compact(self._provider)
+
+    @staticmethod
+    def remove():
+        from diff_gaussian_rasterization import _C
+        _C.set_grad_arena(None, None)
+        _C.set_sh_compact(None)
+
+    def pack_if_needed(self, grads):
+        copied = 0
+        for name in SMALL_ORDER:
+            lo, hi = self.slices[name]
+            g = grads[name]
+            if g is None:
+                self.flat[lo:hi].zero_()
+                copied += 1
+            elif g.data_ptr() != self.flat.data_ptr() + 4 * lo:
+                self.flat[lo:hi].copy_(g.reshape(-1))
+                copied += 1
+        return copied
+
+    def all_reduce(self, means3D, sh_degree):
+        """After every local view's backward: leaves the summed small gradients in `flat` and the summed dL_dsh in
+        `sh_grad` on every rank.  means3D: the [P,3] positions the views were rendered with."""
+        import ctypes
+        import htgs_native as nat
+        if self._next_local != self.views_per_rank:
+            raise RuntimeError(f"{self._next_local} of {self.views_per_rank} local views ran a backward this step")
+        dev = self.device
+        lib = nat.lib()
+        with torch.cuda.device(dev):
+            st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            if self._peer is not None:
+                pm = self._peer
+                pm["hdl"].barrier(channel=0)  # every rank's small gradients and slots are complete
+                if self.collective == "multimem":
+                    nat.check(lib.htgs_allreduce_multimem(ctypes.c_void_p(pm["mc"]), self.rank, self.world, self.n_small_pad, st),
+                              "htgs_allreduce_multimem")
+                    bases = [self.buf.data_ptr()] * self.world  # pushed: every slot is in the local buffer
+                else:
+                    nat.check(lib.htgs_allreduce_p2p(pm["table"], self.rank, self.world, self.n_small_pad, st), "htgs_allreduce_p2p")
+                    bases = pm["ptrs"]  # pulled: slot v is read from its owner over NVLink
+                slots = [bases[v // self.views_per_rank] + 4 * self._slot_offset(v) for v in range(self.views_total)]
+            else:
+                if self.world > 1:
+                    dist.all_reduce(self.buf[:self.n_small_pad], op=dist.ReduceOp.SUM)
+                    lo = self._slot_offset(self.rank * self.views_per_rank)
+                    mine = self.buf[lo:lo + self.views_per_rank * self.slot_floats].clone()
+                    dist.all_gather_into_tensor(self.buf[self.n_small_pad:], mine)
+                slots = [self.buf.data_ptr() + 4 * self._slot_offset(v) for v in range(self.views_total)]
+            arr = (ctypes.c_void_p * self.views_total)(*slots)
+            nat.check(lib.htgs_sh_expand(self.P, int(sh_degree), self.M, self.views_total, means3D.detach().contiguous().data_ptr(), arr,
+                                         self.sh_grad.data_ptr(), st), "htgs_sh_expand")
+            if self._peer is not None:
+                self._peer["hdl"].barrier(channel=0)  # nobody overwrites a slot / the flat buffer while a peer still reads it
+        return self.flat, self.sh_grad
+
+    def grads(self, like):
+        out = {name: self.flat[lo:hi].view_as(like[name]) for name, (lo, hi) in self.slices.items()}
+        out["shs"] = self.sh_grad.view_as(like["shs"])
+        return out

@@ -64,6 +64,15 @@ _SIGNATURES = {
     "htgs_allreduce_p2p": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, ctypes.c_longlong, c_void_p]),
     "htgs_allreduce_multimem": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p]),
     "htgs_allreduce_set_launch_shape": (c_int, [c_int, c_int]),
+    "htgs_sh_slot_floats": (c_size_t, [c_int]),
+    # (P, D, M, R, W, H, bg, means3D, shs, alphas, scales, scale_modifier, rotations, cov3D, view, proj, campos, tanfovx, tanfovy,
+    #  radii, geom, binning, image, dL_dcolor, dL_ddepth, dL_dalpha, scratch, dmeans2D, dopacity, dmeans3D, dcov3D, dscales, drot,
+    #  rgb_slot, is_multicast, stream)
+    "htgs_backward_compact": (c_int, [c_int, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "htgs_sh_expand": (c_int, [c_int, c_int, c_int, c_int, c_void_p, ctypes.POINTER(c_void_p), c_void_p, c_void_p]),
     # (P, D, M, R, W, H, bg, means3D, campos, alphas, radii, geom, binning, image, dL_dcolor, scratch, importance, stream)
     "htgs_importance_accumulate": (c_int, [c_int, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--workload", default="config3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sh-exchange", default="compact", choices=["compact", "full"],
+                    help="--gpus > 1: 'compact' trades the 3-float colour gradient per view and rebuilds dL_dsh on every rank "
+                         "(44 + 12*views B/Gaussian); 'full' all-reduces the flat 59-float gradient (236 B/Gaussian)")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA / CUB / simple-knn A/B legs (N=1 only)")
     ap.add_argument("--no-config4", action="store_true", help="skip the BASELINE config-4 leg (6M Gaussians, 8-view batch, strong scaling)")
     ap.add_argument("--collective", default="auto", choices=["auto", "nccl", "p2p", "multimem"],
@@ -267,33 +270,91 @@ def knn_leg(torch, dev, scene):
     return out
 
 
-def check_allreduce(torch, dist, reducer, rank, world, dev):
-    g = torch.Generator(device=dev).manual_seed(1234 + rank)
-    worst, ok = 0.0, True
-    for it in range(2):  # twice: the second use of the buffer and of the barriers must be as good as the first
-        data = torch.randn(reducer.flat.numel(), generator=g, device=dev)
-        want = data.clone()
-        dist.all_reduce(want, op=dist.ReduceOp.SUM)
-        reducer.flat.copy_(data)
+def make_reducer(args, htgs_dist, P, dev, batch_views, params, world):
+    """Gradient exchange of the view-parallel step: (reducer, compact).  Own kernels over NVLink peer memory / NVSwitch
+    multicast when the ranks can map each other's buffers (torch symmetric memory), NCCL otherwise or with --collective nccl."""
+    if world == 1:
+        return None, False
+    compact = args.sh_exchange == "compact"
+
+    def build(peer):
+        if compact:
+            return htgs_dist.CompactSHGradReducer(P, dev, views_total=batch_views, peer_memory=peer)
+        return htgs_dist.FlatGradReducer(P, dev, peer_memory=peer)
+
+    reducer = None
+    if args.collective != "nccl":
+        try:
+            reducer = build(True if args.collective == "auto" else args.collective)
+        except Exception as e:  # noqa: BLE001 - any failure to set up peer mappings means NCCL
+            if args.collective != "auto":
+                raise
+            print(f"[bench] peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+    if reducer is None:
+        reducer = build(False)
+    if compact:
+        reducer.install(params)
+    else:
+        # gradients land in the all-reduce buffer: the first backward of a step is adopted as .grad in place, further
+        # views of the same step (config4 at < 8 ranks) accumulate into it -- no pack copy either way
+        reducer.install_arena(params)
+    return reducer, compact
+
+
+def remove_reducer(reducer, compact):
+    if reducer is None:
+        return
+    if compact:
+        reducer.remove()
+    else:
+        reducer.remove_arena()
+
+
+def exchange(reducer, compact, params, htgs_dist):
+    if compact:
+        reducer.pack_if_needed({k: params[k].grad for k in htgs_dist.SMALL_ORDER})
+        reducer.all_reduce(params["means3D"], 3)
+    else:
+        reducer.pack_if_needed({k: params[k].grad for k in htgs_dist.PARAM_ORDER})
         reducer.all_reduce()
+
+
+def check_exchange(torch, dist, htgs_dist, reducer, compact, params, one_step, rank, world, dev):
+    """Correctness of the gradient exchange on THIS box, before anything is timed.  The reference is the plain path:
+    ordinary backward of this rank's view(s) (no arena, no compact mode), the five gradients packed into one flat buffer
+    and summed by torch.distributed's NCCL all-reduce.  The exchange under test must reproduce it (<= 1e-5 of each tensor's
+    largest entry: the summation orders differ) and leave identical bits on every rank."""
+    remove_reducer(reducer, compact)
+    one_step(False)
+    ref = htgs_dist.FlatGradReducer(params["means3D"].shape[0], dev)
+    ref.pack({k: params[k].grad for k in htgs_dist.PARAM_ORDER})
+    ref.all_reduce()
+    want = {k: v.clone() for k, v in ref.unpack(params).items()}
+    del ref
+    if compact:
+        reducer.install(params)
+    else:
+        reducer.install_arena(params)
+    worst, same = 0.0, True
+    for _ in range(2):  # twice: the second use of the buffers and barriers must be as good as the first
+        one_step(True)
         torch.cuda.synchronize(dev)
-        got = reducer.flat
-        if world == 2:
-            good = bool(torch.equal(got, want))
-            rel = 0.0 if good else float((got - want).abs().max() / want.abs().max())
-        else:
-            rel = float((got - want).abs().max() / want.abs().max())
-            good = rel <= 1e-6
-        worst, ok = max(worst, rel), ok and good
-    t = torch.tensor([0.0 if ok else 1.0, worst], device=dev, dtype=torch.float64)
+        got = reducer.grads(params) if compact else reducer.unpack(params)
+        for k in htgs_dist.PARAM_ORDER:
+            worst = max(worst, float((got[k] - want[k]).abs().max() / want[k].abs().max().clamp_min(1e-30)))
+            lo, hi = got[k].clone(), got[k].clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            same = same and bool(torch.equal(lo, hi))
+    t = torch.tensor([worst, 0.0 if same else 1.0], device=dev, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    res = {"ok": bool(t[0].item() == 0.0), "max_rel": float(t[1].item()), "collective": reducer.collective,
-           "against": "torch.distributed all_reduce (NCCL), same rank-seeded data, 2 rounds, every rank",
-           "bar": "bit-equal" if world == 2 else "<= 1e-6 relative"}
-    reducer.flat.zero_()
+    res = {"ok": bool(t[0].item() <= 1e-5 and t[1].item() == 0.0), "max_rel": float(t[0].item()), "replicas_bit_identical": bool(t[1].item() == 0.0),
+           "exchange": ("compact SH: 11-float all-reduce + colour-gradient slots, " if compact else "flat 59-float all-reduce, ") + reducer.collective,
+           "against": "plain backward + torch.distributed all_reduce (NCCL) of the flat 59-float gradient, same views, every rank",
+           "bar": "<= 1e-5 of each tensor's largest entry, identical bits on all ranks"}
     if not res["ok"]:
         if rank == 0:
-            print(json.dumps({"error": "gradient all-reduce mismatch", "allreduce_check": res}), file=sys.stderr, flush=True)
+            print(json.dumps({"error": "gradient exchange mismatch", "allreduce_check": res}), file=sys.stderr, flush=True)
         raise SystemExit(3)
     return res
 
@@ -312,22 +373,14 @@ def config4_leg(args, torch, dist, nat, syn, dgr, htgs_dist, rank, world, local_
     params = {k: v.to(dev).requires_grad_(True) for k, v in scene.items()}
     upg = {k: v.to(dev) for k, v in up.items()}
     bg = torch.zeros(3, device=dev)
-    reducer = None
-    if world > 1:
-        if args.collective != "nccl":
-            try:
-                reducer = htgs_dist.FlatGradReducer(P, dev, peer_memory=True if args.collective == "auto" else args.collective)
-            except Exception:  # noqa: BLE001
-                if args.collective != "auto":
-                    raise
-        if reducer is None:
-            reducer = htgs_dist.FlatGradReducer(P, dev)
-        reducer.install_arena(params)
+    reducer, compact = make_reducer(args, htgs_dist, P, dev, 8, params, world)
     ar = []
 
     def step(timed_ar):
         for p in params.values():
             p.grad = None
+        if compact:
+            reducer.begin_step()
         for cam in cams:
             rs = dgr.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], bg=bg,
                                                    scale_modifier=1.0, viewmatrix=cam["viewmatrix"], projmatrix=cam["projmatrix"],
@@ -337,10 +390,9 @@ def config4_leg(args, torch, dist, nat, syn, dgr, htgs_dist, rank, world, local_
                                                                    shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
             torch.autograd.backward((color, depth, alpha), (upg["dL_dcolor"], upg["dL_ddepth"], upg["dL_dalpha"]))
         if world > 1:
-            reducer.pack_if_needed({k: params[k].grad for k in htgs_dist.PARAM_ORDER})
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a0.record()
-            reducer.all_reduce()
+            exchange(reducer, compact, params, htgs_dist)
             a1.record()
             if timed_ar:
                 ar.append((a0, a1))
@@ -365,11 +417,12 @@ def config4_leg(args, torch, dist, nat, syn, dgr, htgs_dist, rank, world, local_
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ar_ms = float(t[0].item()), float(t[1].item())
     finally:
-        if reducer is not None:
-            reducer.remove_arena()
+        remove_reducer(reducer, compact)
+    bytes_per_gaussian = (44 + 12 * 8) if compact else 236
     return {"views_s": 8e3 / ms, "ms_per_step": ms, "allreduce_ms": ar_ms if world > 1 else None, "views_per_step": 8,
             "views_per_step_per_gpu": len(cams), "P": P, "W": W, "H": H, "steps": steps, "warmup": warm, "scaling": "strong",
-            "allreduce_bytes": 236 * P if world > 1 else 0, "collective": reducer.collective if reducer is not None else None}
+            "exchange_bytes": bytes_per_gaussian * P if world > 1 else 0,
+            "exchange": (("compact SH, " if compact else "flat 59-float all-reduce, ") + reducer.collective) if reducer is not None else None}
 
 
 def htgs_dist_shard(n, rank, world):
@@ -403,23 +456,7 @@ def run_ours(args, rank, world, local_rank):
     cams_d = [{k: (v.to(dev) if hasattr(v, "to") else v) for k, v in c.items()} for c in cams_h]
     cam_d = cams_d[0]
     import htgs_dist
-    reducer = None
-    if world > 1:
-        # gradient all-reduce: this library's own kernel over NVLink peer memory / NVSwitch multicast when the ranks
-        # can map each other's buffers (torch symmetric memory), NCCL otherwise or with --collective nccl
-        if args.collective != "nccl":
-            try:
-                reducer = htgs_dist.FlatGradReducer(P, dev, peer_memory=True if args.collective == "auto" else args.collective)
-            except Exception as e:  # noqa: BLE001 - any failure to set up peer mappings means NCCL
-                if args.collective != "auto":
-                    raise
-                print(f"[bench] peer-memory all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
-        if reducer is None:
-            reducer = htgs_dist.FlatGradReducer(P, dev)
-    if reducer is not None:
-        # gradients land in the all-reduce buffer: the first backward of a step is adopted as .grad in place, further
-        # views of the same step (config4 at < 8 ranks) accumulate into it -- no pack copy either way
-        reducer.install_arena(params)
+    reducer, compact = make_reducer(args, htgs_dist, P, dev, batch_views, params, world)
 
     def settings(cam):
         return dgr.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
@@ -429,10 +466,13 @@ def run_ours(args, rank, world, local_rank):
 
     ar_events = []  # (start, end) CUDA event pairs around the gradient all-reduce, filled while `ar_timing` is on
     ar_timing = {"on": False}
+    step_opts = {"skip_exchange": False}
 
     def step(cam, upg, before_backward=None):
         for p in params.values():
             p.grad = None
+        if compact:
+            reducer.begin_step()
         for cam_v in ([cam] if len(cams_d) == 1 else cams_d):
             means2D = torch.zeros_like(params["means3D"], requires_grad=True)
             rast = dgr.GaussianRasterizer(settings(cam_v))
@@ -441,16 +481,15 @@ def run_ours(args, rank, world, local_rank):
             if before_backward is not None:
                 before_backward()
             torch.autograd.backward((color, depth, alpha), (upg["dL_dcolor"], upg["dL_ddepth"], upg["dL_dalpha"]))
-        if world > 1:
-            reducer.pack_if_needed({k: params[k].grad for k in htgs_dist.PARAM_ORDER})
+        if world > 1 and not step_opts["skip_exchange"]:
             if ar_timing["on"]:
                 a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a0.record()
-                reducer.all_reduce()
+                exchange(reducer, compact, params, htgs_dist)
                 a1.record()
                 ar_events.append((a0, a1))
             else:
-                reducer.all_reduce()
+                exchange(reducer, compact, params, htgs_dist)
         return color, radii
 
     def barrier():
@@ -463,7 +502,14 @@ def run_ours(args, rank, world, local_rank):
     # <= 1e-6 relative from 3 ranks up, where the switch / NCCL pick their own summation order) ----
     allreduce_check = None
     if world > 1:
-        allreduce_check = check_allreduce(torch, dist, reducer, rank, world, dev)
+        def one_step(with_exchange):
+            step_opts["skip_exchange"] = not with_exchange
+            try:
+                step(cam_d, up_d)
+            finally:
+                step_opts["skip_exchange"] = False
+
+        allreduce_check = check_exchange(torch, dist, htgs_dist, reducer, compact, params, one_step, rank, world, dev)
 
     # the clock sampler (nvidia-smi/NVML start-up takes ~100 ms and takes driver locks) is started
     # BEFORE the warm-up so that only its steady 200 ms polling overlaps the timed region
@@ -579,8 +625,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- BASELINE config 4 (6M Gaussians, 8-view batch, strong scaling) as an extra leg of the default run ----
     config4 = None
-    if reducer is not None:
-        reducer.remove_arena()
+    remove_reducer(reducer, compact)
     if args.workload == "config3" and not args.no_config4:
         try:
             config4 = config4_leg(args, torch, dist, nat, syn, dgr, htgs_dist, rank, world, local_rank)
@@ -686,15 +731,16 @@ def run_ours(args, rank, world, local_rank):
                    "pairs_tested_after_culling": n_ours_tested, "pairs_blended": n_blended,
                    "warp_visits_by_blending_lanes": visit_hist, "instances_with_empty_reach": stats_h[10],
                    "l2": "inputs+outputs per step (~0.7 GB) exceed the 126 MB L2; no explicit flush",
-                   "parallelism": f"view-parallel dp{world}" + (f" + all-reduce of 59 f32/Gaussian ({reducer.collective})" if world > 1 else "")},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (len(cams_d) * (3 + 2 + passes + 2 + 2) + (1 if world > 1 else 0)),
+                   "parallelism": f"view-parallel dp{world}" + ((" + compact SH exchange: 11 f32/Gaussian all-reduced, 3 f32/Gaussian/view traded, dL_dsh rebuilt on every rank"
+                                                                 if compact else " + all-reduce of 59 f32/Gaussian") + f" ({reducer.collective})" if world > 1 else "")},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (len(cams_d) * (3 + 2 + passes + 2 + 2 + (1 if compact else 0)) + ((2 if compact else 1) if world > 1 else 0)),
         "roofline": roofline, "roofline_hbm": roofline_hbm, "roofline_blend": roofline_blend, "roofline_stages": stage_report,
         "impl": "ours",
     }
     if world > 1:
         out["allreduce_check"] = allreduce_check
         out["allreduce_ms"] = allreduce_ms
-        out["allreduce_bytes"] = 236 * P
+        out["exchange_bytes"] = ((44 + 12 * batch_views) if compact else 236) * P
     if config4 is not None:
         out["config4"] = config4
     # ---- A/B legs against the reference's own CUDA code and the libraries it calls (N = 1 only, after the timed region) ----

@@ -243,6 +243,29 @@ int htgs_allreduce_p2p(const void* const* peer_buffers, int rank, int world, lon
  * replicates the store (multimem.st), so each GPU moves about one buffer per direction at any world size.  The
  * summation order inside the switch is the hardware's; all ranks still receive the same bits. */
 int htgs_allreduce_multimem(void* multicast_buffer, int rank, int world, long long numel, void* stream);
+/* ---- view-parallel steps without shipping the expanded SH gradient (opt-in, no reference counterpart) ----
+ * Per view dL/dsh[i][k][c] = basis_k(direction of Gaussian i from the camera) * r[i][c] with r the clamp-masked colour
+ * gradient, so ranks exchange r (12 B/Gaussian/view) instead of 192 B/Gaussian and each rebuilds the sum itself.
+ *   htgs_sh_slot_floats(P)   floats in one view slot: r of P Gaussians (rows padded to a multiple of 4) + camera position.
+ *   htgs_backward_compact    htgs_backward on the SH path, except that dL_dsh is not produced: r and campos are written to
+ *                            rgb_slot (16-byte aligned, htgs_sh_slot_floats(P) floats) right after the blend backward.  With
+ *                            rgb_slot_is_multicast != 0 the slot address is an NVSwitch multicast address and the writes are
+ *                            multimem.st: the slot arrives in every rank's buffer (the caller provides the cross-GPU barrier
+ *                            before anyone reads, as for htgs_allreduce_multimem).
+ *   htgs_sh_expand           dL_dsh[P,M,3] = sum over the n_views slots (HOST array of device pointers, local or peer-mapped,
+ *                            <= 16) of basis (x) r, in slot order -- identical bits on every rank that passes the same order. */
+size_t htgs_sh_slot_floats(int P);
+int htgs_backward_compact(int P, int D, int M, int64_t R, int W, int H, const float* background, const float* means3D,
+                          const float* shs, const float* alphas, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                          const float* campos, float tanfovx, float tanfovy, const int* radii, const void* geom_buf,
+                          const void* binning_buf, const void* image_buf, const float* dL_dout_color, const float* dL_dout_depth,
+                          const float* dL_dout_alpha, void* scratch, float* dL_dmeans2D, float* dL_dopacity, float* dL_dmeans3D,
+                          float* dL_dcov3D, float* dL_dscales, float* dL_drotations, float* rgb_slot, int rgb_slot_is_multicast,
+                          void* stream);
+int htgs_sh_expand(int P, int D, int M, int n_views, const float* means3D, const float* const* slots_host, float* dL_dsh,
+                   void* stream);
+
 /* Tuning aid for htgs_allreduce_multimem: CTAs per SM (1..16, default 2) and threads per CTA (32..512, default 512)
  * of its kernel, process-wide.  Measured flat on 4 and 8 B200s (0.57-0.60 ms for 236 MB at every shape). */
 int htgs_allreduce_set_launch_shape(int ctas_per_sm, int threads);
