@@ -89,3 +89,18 @@ def load():
     ns.stubbed = missing
     _loaded = ns
     return ns
+
+
+_trainer = None
+
+
+def load_trainer():
+    """The reference's trainer module (trainer/ht3dgs_trainer.py), unchanged.  Its base module asks torch.hub for the MiDaS
+    help text at import time (trainer/trainer.py:40, needs the network): that one call is made a no-op."""
+    global _trainer
+    if _trainer is None:
+        load()
+        import torch
+        torch.hub.help = lambda *a, **k: None
+        _trainer = importlib.import_module("trainer.ht3dgs_trainer")
+    return _trainer

@@ -16,7 +16,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = os.environ.get("HTGS_REFERENCE", "/root/reference")
 DST = os.path.join(ROOT, "baseline", "_ref", "htgs_callers")
-PACKAGES = ("gaussian_renderer", "scene", "utils", "arguments")
+PACKAGES = ("gaussian_renderer", "scene", "utils", "arguments", "trainer")
 
 
 def stage():
