@@ -73,6 +73,7 @@ sort_hist_kernel(const uint64_t* __restrict__ keys, int64_t n, const uint32_t* _
 #pragma unroll
         for (int u = 0; u < HU; u++) {
             if (i0 + u * stride >= n) break;
+            // (warp-aggregating equal low words with match.any before the atomics was measured: 0.229 -> 0.240 ms for the sort)
             for (int p = 0; p < passes; p++) {
                 const int nb = min(8, end_bit - 8 * p);
                 const uint32_t d = (uint32_t)(k[u] >> (8 * p)) & ((1u << nb) - 1u);
@@ -130,7 +131,11 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
 #pragma unroll
     for (int w = 0; w < SORT_WARPS; w++) s_whist[w][tid] = 0;
+    // per-warp digit mask words of the tile-id passes: they borrow the front of the key staging buffer, which is not
+    // written before the ranking is over (8 warps x 256 words = 8 KB of its 32 KB)
+    for (int i = tid; i < SORT_WARPS * SORT_RADIX; i += SORT_THREADS) reinterpret_cast<uint32_t*>(s_keys)[i] = 0;
     __syncthreads();
+    const uint32_t wmask_base = (uint32_t)__cvta_generic_to_shared(s_keys) + (uint32_t)warp * (SORT_RADIX * 4u);
     const uint32_t tile = s_tile;
     const int64_t base = (int64_t)tile * SORT_TILE;
     if (n_dev) n = min(n, (int64_t)*n_dev);  // grid was sized for the capacity; surplus tiles leave
@@ -146,21 +151,54 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
         const int64_t idx = my0 + i * 32;
         k[i] = idx < n ? kin[idx] : ~0ull;
     }
-    // rank inside the warp's 512-key slice (stable: item order = i-major, lane-minor)
+    // Rank inside the warp's 512-key slice (stable: item order = i-major, lane-minor).  ncu (r02) showed the warps of this
+    // kernel stalled on the latency of match.any and of the dependent shared-memory read-modify-write behind it (issue
+    // slots 25-40 % busy), so the three steps run as three waves with 8 independent items in flight each:
+    //   A  peers = match.any(digit)                                   8 independent MATCH
+    //   B  the lowest peer adds the group size to the warp's digit counter with ONE shared-memory atomic and keeps the old
+    //      value; atomics of one warp to one address retire in issue order, so item i's prefix counts items < i exactly
+    //   C  the old value is broadcast from the leader; rank = old + number of peers in lower lanes
+    //
+    // Step A has two forms.  match.any costs about one cycle of a shared unit per DISTINCT value in the warp
+    // (tools/micro/match_probe.cu: 5 -> 26 cycles for 1 -> 32 distinct).  In the depth-byte passes neighbouring keys are
+    // the tile instances of one Gaussian (same depth, so the same digit: ~8 distinct values per warp) and it is the cheap
+    // form; in the tile-id passes (shift >= 32) the 32 digits of a warp are nearly all different, which made those two
+    // passes 46-56 us against 30-36 us.  There the peers are found through shared memory instead: every lane ORs its lane
+    // bit into a per-digit mask word, reads the word back and clears it -- three shared-memory instructions that are
+    // conflict-free exactly when the digits differ, issued back to back (a warp's shared-memory instructions execute in
+    // program order, so the read sees every lane's bit and the clear comes after every lane's read).
     uint16_t pos[SORT_IPT];
+#ifdef HTGS_SORT_SMEM_ALL
+    const bool via_smem = true;
+#else
+    const bool via_smem = shift >= 32;
+#endif
 #pragma unroll
-    for (int i = 0; i < SORT_IPT; i++) {
-        const uint32_t d = (uint32_t)(k[i] >> shift) & mask;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(peers) - 1;
-        uint32_t prev = 0;
-        if (lane == leader) {
-            prev = s_whist[warp][d];
-            s_whist[warp][d] = prev + __popc(peers);
+    for (int h = 0; h < SORT_IPT; h += 8) {
+        uint32_t peers[8], prev[8];
+        if (via_smem) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const uint32_t a = wmask_base + (((uint32_t)(k[h + i] >> shift) & mask) << 2);
+                asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(a), "r"(1u << lane) : "memory");
+                asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(peers[i]) : "r"(a) : "memory");
+                asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(a), "r"(0u) : "memory");
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) peers[i] = __match_any_sync(0xffffffffu, (uint32_t)(k[h + i] >> shift) & mask);
         }
-        prev = __shfl_sync(0xffffffffu, prev, leader);
-        pos[i] = (uint16_t)(prev + __popc(peers & lanemask_lt));
-        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint32_t d = (uint32_t)(k[h + i] >> shift) & mask;
+            prev[i] = 0;
+            if ((peers[i] & lanemask_lt) == 0) prev[i] = atomicAdd(&s_whist[warp][d], (uint32_t)__popc(peers[i]));  // lowest peer
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint32_t p0 = __shfl_sync(0xffffffffu, prev[i], __ffs(peers[i]) - 1);
+            pos[h + i] = (uint16_t)(p0 + __popc(peers[i] & lanemask_lt));
+        }
     }
     __syncthreads();
 
