@@ -346,13 +346,15 @@ static int backward_impl(const char* who, const float* shs_rest, const float* op
         if (launch_blend_backward(P, W, H, img.ranges, b.values_sorted, g, background, alphas, img.n_contrib, dL_dout_color,
                                   dL_dout_depth, dL_dout_alpha, gacc, st)) return 1;
     }
-    // compact SH mode: the clamp-masked colour gradient leaves for its view slot as soon as the blend backward is done
+    // compact SH mode: the clamp-masked colour gradient leaves for its view slot as soon as the blend backward is done, on a
+    // side stream beside the geometry backward (joined below)
     if (rgb_slot && launch_rgb_extract(P, gacc, g.clamped, campos, rgb_slot, rgb_multicast, st)) return 1;
     // the SH path feeds dL/dcolour into dL/dsh; only the precomputed-colour path returns it
     StageTimer t(ST_GEOM_BWD, st);
     if (launch_geom_backward(P, D, M, means3D, radii, shs, shs_rest, opacity_raw, dL_dsh_rest, colors_precomp, scales, scale_modifier, rotations, cov3D_precomp,
                              viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, g, gacc, dL_dmeans2D, dL_dopacity,
                              dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, st)) return 1;
+    if (rgb_slot && join_rgb_extract(st)) return 1;  // the stream the caller sees again orders everything, the push included
     return 0;
 }
 

@@ -91,6 +91,7 @@ int launch_geom_backward(int P, int D, int M, const float* means3D, const int* r
 
 int launch_rgb_extract(int P, const float* gacc, const uint8_t* clamped, const float* campos, float* slot, bool multicast,
                        cudaStream_t st);
+int join_rgb_extract(cudaStream_t st);
 
 size_t sort_scratch_bytes(int64_t n);
 int sort_pairs(int64_t n, int end_bit, uint64_t* k_in, uint32_t* v_in, uint64_t* k_out, uint32_t* v_out,

@@ -16,6 +16,7 @@
 // Slot layout (floats): [0 .. 3*P4) r of Gaussians 0..P4-1 (P4 = P rounded up to 4), [3*P4 .. 3*P4+4) camera position + pad.
 #include "../../include/htgs.h"
 #include "sh_basis.cuh"
+#include <mutex>
 
 namespace htgs {
 
@@ -31,33 +32,36 @@ __device__ __forceinline__ void store4(float* a, float4 v, bool mc) {
         *reinterpret_cast<float4*>(a) = v;
 }
 
-// one thread per 4 Gaussians: 4 accumulator rows in, three 128-bit stores out
+// 256 threads per 1024 Gaussians.  Each thread gathers r of 4 Gaussians (4 accumulator rows in) into shared memory; the CTA
+// then writes its 3072 floats as 768 consecutive 128-bit stores, lane after lane -- full 128-byte lines per warp, which is
+// what the NVLink multicast path wants (the first version let every thread store its own three float4: a 48-byte lane
+// stride, a third of every line per instruction, and on 8 GPUs the push cost as much as the all-reduce it replaced).
+constexpr int RGB_CTA_GAUSS = 1024;
 __global__ void __launch_bounds__(256)
 rgb_extract_kernel(int P, const float* __restrict__ gacc, const uint8_t* __restrict__ clamped, const float* __restrict__ campos,
                    float* __restrict__ slot, bool multicast) {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ __align__(16) float s_r[3 * RGB_CTA_GAUSS];
     const int P4 = (P + 3) & ~3;
-    if (q == 0) store4(slot + 3 * (size_t)P4, make_float4(campos[0], campos[1], campos[2], 0.f), multicast);
-    const int i0 = 4 * q;
-    if (i0 >= P) return;
-    float r[12];
+    if (blockIdx.x == 0 && threadIdx.x == 0) store4(slot + 3 * (size_t)P4, make_float4(campos[0], campos[1], campos[2], 0.f), multicast);
+    const int base = blockIdx.x * RGB_CTA_GAUSS;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-        const int i = i0 + j;
+        const int li = j * 256 + threadIdx.x;  // consecutive lanes read consecutive accumulator rows
+        const int i = base + li;
         float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
         uint32_t cl = 0;
         if (i < P) {
             g = reinterpret_cast<const float4*>(gacc + (size_t)i * 12)[2];
             cl = clamped[i];
         }
-        r[3 * j] = (cl & 1) ? 0.f : g.x;
-        r[3 * j + 1] = (cl & 2) ? 0.f : g.y;
-        r[3 * j + 2] = (cl & 4) ? 0.f : g.z;
+        s_r[3 * li] = (cl & 1) ? 0.f : g.x;
+        s_r[3 * li + 1] = (cl & 2) ? 0.f : g.y;
+        s_r[3 * li + 2] = (cl & 4) ? 0.f : g.z;
     }
-    float* o = slot + 3 * (size_t)i0;
-    store4(o, make_float4(r[0], r[1], r[2], r[3]), multicast);
-    store4(o + 4, make_float4(r[4], r[5], r[6], r[7]), multicast);
-    store4(o + 8, make_float4(r[8], r[9], r[10], r[11]), multicast);
+    __syncthreads();
+    const int n4 = (min(RGB_CTA_GAUSS, P4 - base) * 3) / 4;  // float4 this CTA owns (P4 is a multiple of 4, so is the count)
+    float* o = slot + 3 * (size_t)base;
+    for (int q = threadIdx.x; q < n4; q += 256) store4(o + 4 * q, reinterpret_cast<const float4*>(s_r)[q], multicast);
 }
 
 __global__ void __launch_bounds__(128)
@@ -102,11 +106,55 @@ sh_expand_kernel(int P, int D, int M, int n_views, const float* __restrict__ mea
     }
 }
 
+// The extraction (and, with a multicast slot, the push over NVLink) needs only the blend backward's accumulator, so it
+// runs on a side stream NEXT TO the geometry backward: forked from the caller's stream after the blend backward, joined
+// back before the entry point returns control of the stream.  One side stream and one event pair per device, created
+// on first use under a lock (process-global state, listed in include/htgs.h); compact-mode backwards on one device must
+// therefore come from one stream at a time.
+namespace {
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+SideStream g_side[64];
+std::mutex g_side_mutex;
+
+int side_for_current_device(SideStream** out) {
+    int dev = -1;
+    HTGS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("compact SH mode: device ordinal %d not supported (max 63)", dev); return 1; }
+    std::lock_guard<std::mutex> lock(g_side_mutex);
+    SideStream& s = g_side[dev];
+    if (!s.stream) {
+        cudaStream_t st = nullptr;
+        cudaEvent_t a = nullptr, b = nullptr;
+        HTGS_CUDA_CHECK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        HTGS_CUDA_CHECK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        HTGS_CUDA_CHECK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        s.fork = a; s.join = b; s.stream = st;
+    }
+    *out = &s;
+    return 0;
+}
+}  // namespace
+
 int launch_rgb_extract(int P, const float* gacc, const uint8_t* clamped, const float* campos, float* slot, bool multicast,
                        cudaStream_t st) {
-    const int quads = (P + 3) / 4;
-    rgb_extract_kernel<<<(quads + 255) / 256, 256, 0, st>>>(P, gacc, clamped, campos, slot, multicast);
+    SideStream* side = nullptr;
+    if (side_for_current_device(&side)) return 1;
+    HTGS_CUDA_CHECK(cudaEventRecord(side->fork, st));
+    HTGS_CUDA_CHECK(cudaStreamWaitEvent(side->stream, side->fork, 0));
+    rgb_extract_kernel<<<(P + RGB_CTA_GAUSS - 1) / RGB_CTA_GAUSS, 256, 0, side->stream>>>(P, gacc, clamped, campos, slot, multicast);
     HTGS_LAUNCH_CHECK("rgb_extract_kernel");
+    HTGS_CUDA_CHECK(cudaEventRecord(side->join, side->stream));
+    return 0;
+}
+
+// makes the caller's stream wait for the side-stream work of the last launch_rgb_extract on this device
+int join_rgb_extract(cudaStream_t st) {
+    SideStream* side = nullptr;
+    if (side_for_current_device(&side)) return 1;
+    HTGS_CUDA_CHECK(cudaStreamWaitEvent(st, side->join, 0));
     return 0;
 }
 

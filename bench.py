@@ -561,7 +561,11 @@ def run_ours(args, rank, world, local_rank):
         # the camera (view 16 + projection 16 + position 3 floats) travels as ONE pinned buffer / one copy
         host_cam = torch.cat([cam_h[k].reshape(-1).float() for k in ("viewmatrix", "projmatrix", "campos")]).pin_memory()
         h2d = sum(v.numel() * 4 for v in host.values()) + host_cam.numel() * 4
-        result = torch.zeros(1, dtype=torch.float64).pin_memory()
+        # the step's scalar result travels device -> pinned host memory asynchronously behind an event; the host consumes it
+        # one step later (a training loop logs its loss the same way), so the read never drains the GPU's queue
+        results = [torch.zeros(1, dtype=torch.float64).pin_memory() for _ in range(2)]
+        arrived = [torch.cuda.Event(), torch.cuda.Event()]
+        seen = {"last": 0.0}
 
         # Input pipeline of the end-to-end leg (every step's inputs still come from pinned host memory, every step's
         # result is still read back with a blocking copy -- only WHEN the upload runs changes):
@@ -602,8 +606,12 @@ def run_ours(args, rank, world, local_rank):
             color, radii = step(cam, staged[slot], before_backward=lambda: main.wait_event(uploaded[slot]))
             consumed[slot].record(main)
             s = (color.detach().sum(dtype=torch.float64) + params["opacities"].grad.sum(dtype=torch.float64)).reshape(1)
-            result.copy_(s, non_blocking=False)  # device->host read of the step's scalar result
-            return float(result[0].detach())
+            results[slot].copy_(s, non_blocking=True)  # device->host read of the step's scalar result
+            arrived[slot].record(main)
+            if state["k"] > 1:  # consume the previous step's result (waits only if it has not arrived yet)
+                arrived[slot ^ 1].synchronize()
+                seen["last"] = float(results[slot ^ 1][0])
+            return seen["last"]
 
         for _ in range(3):
             e2e_step()
@@ -620,7 +628,8 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": batch_views * args.steps / dt, "unit": "views/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 8,
                "ms_per_step": 1e3 * dt / args.steps,
                "h2d": "camera (140 B) + the three upstream-gradient images, pinned host memory, every step",
-               "d2h": "checksum only: one float64 = sum(colour image) + sum(dL/dopacity), read back blocking every step; the "
+               "d2h": "checksum only: one float64 = sum(colour image) + sum(dL/dopacity) per step, copied to pinned host memory "
+                      "behind an event and consumed by the host one step later (all reads complete inside the timed region); the "
                       "Gaussian parameters stay resident on the device, as in a training loop"}
 
     # ---- BASELINE config 4 (6M Gaussians, 8-view batch, strong scaling) as an extra leg of the default run ----

@@ -27,7 +27,10 @@
  *     exceptions, each documented at its declaration: the built-in scratch
  *     array of htgs_sort_pairs_static (shared per device), the SSIM window
  *     constants of htgs_l1_ssim_* (uploaded once per device under a lock, first
- *     call outside stream capture), the launch-shape override of
+ *     call outside stream capture), the side stream + event pair of
+ *     htgs_backward_compact (one per device, created on first use under a
+ *     lock; compact-mode backwards on a device come from one stream at a
+ *     time), the launch-shape override of
  *     htgs_allreduce_set_launch_shape, and the htgs_profile_* stage timers
  *     (process-wide measurement aid, not thread-safe).
  */
