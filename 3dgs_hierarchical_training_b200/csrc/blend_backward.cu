@@ -56,14 +56,12 @@ constexpr int ACC_STRIDE = 12;   // per-Gaussian tile sums: [0..5] moments 1,x,y
 //                     12..15 the low parts (d - hi) of the same four
 //                   With B = w the rows 0..5 give the six moments (rows 8..15 are ignored); with B = aT rows 8..11 +
 //                   rows 12..15 give the colour / depth sums (rows 0..7 are ignored).
-//   slot[v]         batch index of the Gaussian behind visit v of the open phase
 constexpr int PH_ROW_AT = 8, PH_PARK_ROWS = 16, PH_KSTEPS = 4;
 struct __align__(16) WarpPhase {
     float park[PH_PARK_ROWS][PH_STRIDE];   // 2304 B
     float4 afrag[PH_KSTEPS][32];           // 2048 B
-    uint32_t slot[PH_N];
 };
-constexpr uint32_t PH_OFF_AFRAG = PH_PARK_ROWS * PH_STRIDE * 4, PH_OFF_SLOT = PH_OFF_AFRAG + PH_KSTEPS * 32 * 16;
+constexpr uint32_t PH_OFF_AFRAG = PH_PARK_ROWS * PH_STRIDE * 4;
 
 __device__ __forceinline__ void sts32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
 __device__ __forceinline__ void sts32u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
@@ -95,7 +93,7 @@ __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) 
 // One tensor-core phase of a warp: sums the parked (w, aT) of `cnt` <= 8 visits over the warp's 32 pixels against the
 // per-pixel constants and adds the 10 x cnt results into the batch accumulator rows.  ph = shared address of the
 // warp's WarpPhase, acc = shared address of s_acc.  Warp-collective (all 32 lanes, converged).
-__device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, int cnt, int lane) {
+__device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, int cnt, int lane, uint64_t slots) {
     __syncwarp();
     const int g = lane >> 2, t = lane & 3;
     const uint32_t aw = ph + (uint32_t)g * (PH_STRIDE * 4u) + (uint32_t)t * 32u;   // visit g, pixels t*8 .. t*8+7
@@ -132,9 +130,10 @@ __device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, int cnt,
     float y0 = ca1[2] + ca2[2], y1 = ca1[3] + ca2[3];         // colour/depth row g+8: high-part rows for g < 4, low-part rows above
     y0 += __shfl_xor_sync(0xffffffffu, y0, 16);               // lane g+4 holds the low-part row of the same quantity
     y1 += __shfl_xor_sync(0xffffffffu, y1, 16);
-    uint32_t s0, s1;
-    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(s0), "=r"(s1) : "r"(ph + PH_OFF_SLOT + (uint32_t)t * 8u) : "memory");
+    // batch index of the Gaussian behind each visit: one byte per visit, the latest visit in the lowest byte
     const bool v0 = 2 * t < cnt, v1 = 2 * t + 1 < cnt;
+    const uint32_t s0 = (uint32_t)(slots >> (8 * ((cnt - 1 - 2 * t) & 7))) & 0xffu;
+    const uint32_t s1 = (uint32_t)(slots >> (8 * ((cnt - 2 - 2 * t) & 7))) & 0xffu;
     float* accp = reinterpret_cast<float*>(__cvta_shared_to_generic((size_t)acc));
     if (g < 6) {
         if (v0 && x0 != 0.f) atomicAdd(accp + s0 * ACC_STRIDE + g, x0);
@@ -190,9 +189,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     // -(T_final * bg . dL/dpixel): numerator of the background term, backward.cu:575-578
     const float bg_k = -T_final * (bg[0] * d0 + bg[1] * d1 + bg[2] * d2);
     const bool warp_has_bg = __any_sync(0xffffffffu, bg_k != 0.f);
-    // A = sum_ch accum_rec[ch]*dL/dch (colour, depth, alpha channels); Cprev = the same dot product
-    // for the previously visited Gaussian's own colour/depth/1
-    float A = 0.f, Cprev = 0.f, last_alpha = 0.f, one_m_last = 1.f;  // one_m_last = 1 - last_alpha, carried instead of recomputed
+    // A = sum_ch accum_rec[ch]*dL/dch (colour, depth, alpha channels) as the NEXT blended Gaussian will see it: the
+    // reference folds the previous Gaussian's colour in lazily (backward.cu:547-567, last_alpha / last_color carried to
+    // the next iteration); folding it in right after use is the same fma on the same values and carries one float
+    // instead of four
+    float A = 0.f;
 
     // This pixel's column of the A operand, scattered into fragment order: pixel p = lane sits in k-step (p & 7) >> 1,
     // fragment lanes g*4 + (p >> 3) for every row pair (g, g+8), element (p & 1) of the k-step's pixel pair.
@@ -232,10 +233,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     for (int w = 0; w < BLEND_WARPS; w++) block_last = max(block_last, s_warp_last[w]);
 
     const uint64_t pxy = pk2(pxf, pyf), d0_d1 = pk2(d0, d1), d2_dd = pk2(d2, dd), da_0 = pk2(da, 0.f);
-    const uint32_t sg_base = smem_u32(s_g);
-    const uint32_t acc_base = smem_u32(s_acc);
+    // (the bases pass through an opaque asm so that ptxas keeps them in registers: it otherwise rebuilds the shared
+    // window address -- S2UR CgaCtaId, UMOV, UIADD3, ULEA -- inside every visit)
+    uint32_t sg_base, acc_base;
+    asm volatile("mov.u32 %0, %1;" : "=r"(sg_base) : "r"(smem_u32(s_g)));
+    asm volatile("mov.u32 %0, %1;" : "=r"(acc_base) : "r"(smem_u32(s_acc)));
     const uint32_t park = ph + (uint32_t)lane * 4u;                          // this lane's column of the (w | aT) panel
-    const uint32_t slot_base = ph + PH_OFF_SLOT;
 
     for (int base = 0; base < n; base += BWD_BATCH) {
         const int cnt = min(BWD_BATCH, n - base);
@@ -255,7 +258,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         }
         __syncthreads();
         int parked = 0;           // visits parked in the warp's panel since its last tensor-core phase (warp-uniform)
-        uint32_t park_at = park;  // where this lane parks the next visit; the slot word sits at a fixed distance pattern
+        uint64_t slots = 0;       // their batch indices, one byte each, newest in the lowest byte (warp-uniform)
+        uint32_t park_at = park;  // where this lane parks the next visit
         for (int c0 = 0; c0 < cnt; c0 += 32) {
             const int j = c0 + lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1) && (uint32_t)(top - j) < warp_last;
@@ -295,28 +299,25 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     float c_lo, c_hi;
                     up2(fma2(pk2(q2.x, q2.y), d2_dd, fma2(pk2(q1.z, q1.w), d0_d1, da_0)), c_lo, c_hi);
                     const float Cd = c_lo + c_hi;
-                    A = fmaf(last_alpha, Cprev, one_m_last * A);
-                    Cprev = Cd;
-                    last_alpha = alpha;
-                    one_m_last = one_m_a;
                     float dL_dopa = (Cd - A) * T;
+                    A = fmaf(alpha, Cd, one_m_a * A);
                     if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
                     w = G * dL_dopa;
                 }
                 if (__any_sync(0xffffffffu, live)) {
                     sts32(park_at, w);
                     sts32(park_at + (uint32_t)(PH_ROW_AT * PH_STRIDE * 4), aT);
-                    sts32u(slot_base + (uint32_t)parked * 4u, (uint32_t)(c0 + b));  // same value from every lane
+                    slots = (slots << 8) | (uint64_t)(uint32_t)(c0 + b);
                     park_at += (uint32_t)(PH_STRIDE * 4);
                     if (++parked == PH_N) {
-                        reduce_phase(ph, acc_base, PH_N, lane);
+                        reduce_phase(ph, acc_base, PH_N, lane, slots);
                         parked = 0;
                         park_at = park;
                     }
                 }
             }
         }
-        if (parked) reduce_phase(ph, acc_base, parked, lane);
+        if (parked) reduce_phase(ph, acc_base, parked, lane, slots);
         __syncthreads();
         if (tid < cnt) {
             const float4* a4 = reinterpret_cast<const float4*>(&s_acc[tid][0]);
