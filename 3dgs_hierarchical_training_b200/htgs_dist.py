@@ -281,16 +281,14 @@ class CompactSHGradReducer:
     def all_reduce(self, means3D, sh_degree):
         """After every local view's backward: leaves the summed small gradients in `flat` and the summed dL_dsh in
         `sh_grad` on every rank.  means3D: the [P,3] positions the views were rendered with."""
-        import ctypes
-        import htgs_native as nat
         if self._next_local != self.views_per_rank:
             raise RuntimeError(f"{self._next_local} of {self.views_per_rank} local views ran a backward this step")
-        dev = self.device
-        lib = nat.lib()
-        with torch.cuda.device(dev):
-            st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-            if self._peer is not None:
-                pm = self._peer
+        if self._peer is not None:
+            import ctypes
+            import htgs_native as nat
+            pm, dev, lib = self._peer, self.device, nat.lib()
+            with torch.cuda.device(dev):
+                st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
                 pm["hdl"].barrier(channel=0)  # every rank's small gradients and slots are complete
                 if self.collective == "multimem":
                     nat.check(lib.htgs_allreduce_multimem(ctypes.c_void_p(pm["mc"]), self.rank, self.world, self.n_small_pad, st),
@@ -300,19 +298,29 @@ class CompactSHGradReducer:
                     nat.check(lib.htgs_allreduce_p2p(pm["table"], self.rank, self.world, self.n_small_pad, st), "htgs_allreduce_p2p")
                     bases = pm["ptrs"]  # pulled: slot v is read from its owner over NVLink
                 slots = [bases[v // self.views_per_rank] + 4 * self._slot_offset(v) for v in range(self.views_total)]
-            else:
-                if self.world > 1:
-                    dist.all_reduce(self.buf[:self.n_small_pad], op=dist.ReduceOp.SUM)
-                    lo = self._slot_offset(self.rank * self.views_per_rank)
-                    mine = self.buf[lo:lo + self.views_per_rank * self.slot_floats].clone()
-                    dist.all_gather_into_tensor(self.buf[self.n_small_pad:], mine)
-                slots = [self.buf.data_ptr() + 4 * self._slot_offset(v) for v in range(self.views_total)]
-            arr = (ctypes.c_void_p * self.views_total)(*slots)
-            nat.check(lib.htgs_sh_expand(self.P, int(sh_degree), self.M, self.views_total, means3D.detach().contiguous().data_ptr(), arr,
-                                         self.sh_grad.data_ptr(), st), "htgs_sh_expand")
-            if self._peer is not None:
-                self._peer["hdl"].barrier(channel=0)  # nobody overwrites a slot / the flat buffer while a peer still reads it
+                self._expand(slots, means3D, sh_degree)
+                pm["hdl"].barrier(channel=0)  # nobody overwrites a slot / the flat buffer while a peer still reads it
+        else:
+            if self.world > 1:  # torch.distributed transport (NCCL on GPUs; gloo in the CPU tests of this host logic)
+                dist.all_reduce(self.buf[:self.n_small_pad], op=dist.ReduceOp.SUM)
+                lo = self._slot_offset(self.rank * self.views_per_rank)
+                mine = self.buf[lo:lo + self.views_per_rank * self.slot_floats].clone()
+                dist.all_gather_into_tensor(self.buf[self.n_small_pad:], mine)
+            self._expand([self.buf.data_ptr() + 4 * self._slot_offset(v) for v in range(self.views_total)], means3D, sh_degree)
         return self.flat, self.sh_grad
+
+    def _expand(self, slot_addresses, means3D, sh_degree):
+        """sh_grad = sum over the view slots (device addresses, view order) of basis (x) colour gradient: htgs_sh_expand."""
+        import ctypes
+        import htgs_native as nat
+        if not self.sh_grad.is_cuda:
+            raise RuntimeError("CompactSHGradReducer: the SH rebuild is a CUDA kernel; there is no host path")
+        dev = self.device
+        with torch.cuda.device(dev):
+            arr = (ctypes.c_void_p * self.views_total)(*slot_addresses)
+            nat.check(nat.lib().htgs_sh_expand(self.P, int(sh_degree), self.M, self.views_total, means3D.detach().contiguous().data_ptr(), arr,
+                                               self.sh_grad.data_ptr(), ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)),
+                      "htgs_sh_expand")
 
     def grads(self, like):
         out = {name: self.flat[lo:hi].view_as(like[name]) for name, (lo, hi) in self.slices.items()}
