@@ -60,6 +60,8 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P) return;
     const bool sh_vec = dL_dsh != nullptr && ((M * 3) % 4 == 0) && ((reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0);
+    // 256-bit accesses on the 192-byte SH rows (one 32-byte sector per lane and instruction, gs_math.cuh)
+    const bool sh_vec256 = !RAW && sh_vec && M == 16 && ((reinterpret_cast<uintptr_t>(dL_dsh) & 31) == 0);
 
     if (!(radii[idx] > 0)) {
         store3(dL_dmeans2D + 3 * (size_t)idx, 0.f, 0.f, 0.f);
@@ -78,7 +80,11 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
             store_rest_row(dL_dsh_rest, idx, z45);
         } else if (dL_dsh) {
             float* o = dL_dsh + (size_t)idx * M * 3;
-            if (sh_vec) {
+            if (sh_vec256) {
+                const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int i = 0; i < 6; i++) stg256(o + 8 * i, z8);
+            } else if (sh_vec) {
                 for (int i = 0; i < M * 3 / 4; i++) reinterpret_cast<float4*>(o)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             } else {
                 for (int i = 0; i < M * 3; i++) o[i] = 0.f;
@@ -219,6 +225,19 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
             sd[0] = __ldg(shs + 3 * (size_t)idx) * r0 + __ldg(shs + 3 * (size_t)idx + 1) * r1 + __ldg(shs + 3 * (size_t)idx + 2) * r2;
 #pragma unroll
             for (int k = 1; k < 16; k++) sd[k] = e[3 * k - 3] * r0 + e[3 * k - 2] * r1 + e[3 * k - 1] * r2;
+        } else if (fast && ((reinterpret_cast<uintptr_t>(shs) & 31) == 0)) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                if (8 * i < 3 * nact) {
+                    float e[8];
+                    ldg256_nc(sh + 8 * i, e);
+#pragma unroll
+                    for (int t = 0; t < 8; t++) {
+                        const int el = 8 * i + t, k = el / 3, c = el - 3 * k;
+                        sd[k] = fmaf(e[t], c == 0 ? r0 : (c == 1 ? r1 : r2), sd[k]);
+                    }
+                }
+            }
         } else if (fast) {
             const float4* sh4 = reinterpret_cast<const float4*>(sh);
 #pragma unroll
@@ -299,6 +318,21 @@ geom_backward_kernel(int P, int D, int M, const float* __restrict__ means3D, con
         } else if (dL_dsh == nullptr) {
             // compact SH mode (htgs_backward_compact): the expanded 192 B/Gaussian gradient is not written here at all; the
             // clamp-masked colour gradient it is the outer product of has already left through rgb_extract_kernel
+        } else if (fast && sh_vec256) {
+            // six 256-bit stores; coefficient and channel of every element are compile-time
+#pragma unroll
+            for (int k = 1; k < 16; k++)
+                if (k >= ncoef) w[k] = 0.f;
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                float e[8];
+#pragma unroll
+                for (int t = 0; t < 8; t++) {
+                    const int el = 8 * i + t, k = el / 3, c = el - 3 * k;
+                    e[t] = w[k] * (c == 0 ? r0 : (c == 1 ? r1 : r2));
+                }
+                stg256(o + 8 * i, e);
+            }
         } else if (fast && sh_vec) {
             // twelve 128-bit stores; coefficient and channel of every element are compile-time
 #pragma unroll

@@ -16,6 +16,19 @@ namespace htgs {
 #define SB(a, b) __fsub_rn((a), (b))
 #define DV(a, b) __fdiv_rn((a), (b))
 
+// 256-bit global accesses (sm_100: LDG.E.ENL2.256 / STG.E.ENL2.256).  The 192-byte SH rows are read and written by one
+// lane per Gaussian; with 128-bit accesses every instruction touches half of a 32-byte sector per lane, so the memory
+// system sees twice the sector requests (and, for stores, twice the partial-sector writes) the data needs.  One lane-
+// access of 32 bytes is exactly one sector.  Addresses must be 32-byte aligned.
+__device__ __forceinline__ void ldg256_nc(const float* p, float* v) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
+}
+__device__ __forceinline__ void stg256(float* p, const float* v) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]),
+                 "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
+
 // row r of the row-vector 4x4 transform: m[12+r] + fma(z, m[8+r], fma(x, m[r], y*m[4+r]))
 // (auxiliary.h:58-77)
 __device__ __forceinline__ float xform_row(const float* __restrict__ m, int r, float x, float y, float z) {

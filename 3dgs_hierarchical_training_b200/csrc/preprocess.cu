@@ -73,12 +73,16 @@ __device__ __forceinline__ void sh_to_rgb(const float* sh, float x, float y, flo
 }
 
 template <int D>
-__device__ __forceinline__ void load_sh_and_eval(const float* __restrict__ shp, bool vec_ok, float x, float y, float z,
-                                                 float* res) {
+__device__ __forceinline__ void load_sh_and_eval(const float* __restrict__ shp, bool vec_ok, bool vec256_ok, float x, float y,
+                                                 float z, float* res) {
     constexpr int NC = (D + 1) * (D + 1) * 3;
     constexpr int NV = (NC + 3) / 4;
-    float sh[NV * 4];
-    if (vec_ok) {
+    constexpr int NV8 = (NC + 7) / 8;
+    float sh[NV8 * 8];
+    if (vec256_ok) {  // rows of 48 floats starting 32-byte aligned: whole sectors per lane (reads stay inside the row)
+#pragma unroll
+        for (int i = 0; i < NV8; i++) ldg256_nc(shp + 8 * i, sh + 8 * i);
+    } else if (vec_ok) {
         const float4* p4 = reinterpret_cast<const float4*>(shp);
 #pragma unroll
         for (int i = 0; i < NV; i++) {
@@ -193,11 +197,12 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
                 } else {
                 const float* shp = shs + (size_t)idx * M * 3;
                 const bool vec_ok = ((M * 3) % 4 == 0) && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0);
+                const bool v256 = M == 16 && ((reinterpret_cast<uintptr_t>(shs) & 31) == 0);
                 switch (D) {
-                    case 0: load_sh_and_eval<0>(shp, vec_ok && M * 3 >= 4, x, y, z, res); break;
-                    case 1: load_sh_and_eval<1>(shp, vec_ok, x, y, z, res); break;
-                    case 2: load_sh_and_eval<2>(shp, vec_ok && M * 3 >= 28, x, y, z, res); break;
-                    default: load_sh_and_eval<3>(shp, vec_ok, x, y, z, res); break;
+                    case 0: load_sh_and_eval<0>(shp, vec_ok && M * 3 >= 4, v256, x, y, z, res); break;
+                    case 1: load_sh_and_eval<1>(shp, vec_ok, v256, x, y, z, res); break;
+                    case 2: load_sh_and_eval<2>(shp, vec_ok && M * 3 >= 28, v256, x, y, z, res); break;
+                    default: load_sh_and_eval<3>(shp, vec_ok, v256, x, y, z, res); break;
                 }
                 }
 #pragma unroll

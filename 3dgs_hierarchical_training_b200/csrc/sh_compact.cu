@@ -95,7 +95,10 @@ sh_expand_kernel(int P, int D, int M, int n_views, const float* __restrict__ mea
         }
     }
     float* o = dL_dsh + (size_t)idx * M * 3;
-    if (M == 16 && (reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0) {
+    if (M == 16 && (reinterpret_cast<uintptr_t>(dL_dsh) & 31) == 0) {  // one 32-byte sector per lane and store (gs_math.cuh)
+#pragma unroll
+        for (int i = 0; i < 6; i++) stg256(o + 8 * i, acc + 8 * i);
+    } else if (M == 16 && (reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0) {
 #pragma unroll
         for (int i = 0; i < 12; i++) reinterpret_cast<float4*>(o)[i] = make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
     } else {
