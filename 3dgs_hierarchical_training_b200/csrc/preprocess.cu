@@ -126,6 +126,14 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
     int my_radius = 0;
     if (idx < P) {
         const float px = means3D[3 * idx], py = means3D[3 * idx + 1], pz = means3D[3 * idx + 2];
+        // scale and rotation are requested together with the position, before the near-plane test that only 2 % of the
+        // Gaussians fail: one memory round trip less on the dependent chain position -> covariance -> SH row
+        float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+        if (cov3D_precomp == nullptr) {
+            q = reinterpret_cast<const float4*>(rotations)[idx];
+            s0 = scales[3 * idx]; s1 = scales[3 * idx + 1]; s2 = scales[3 * idx + 2];
+        }
         const float depth = xform_row(vm, 2, px, py, pz);
         do {
             if (depth <= 0.2f) {  // auxiliary.h:154
@@ -146,8 +154,6 @@ preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const 
 #pragma unroll
                 for (int k = 0; k < 6; k++) cov3[k] = cov3D_precomp[6 * (size_t)idx + k];
             } else {
-                float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-                float s0 = scales[3 * idx], s1 = scales[3 * idx + 1], s2 = scales[3 * idx + 2];
                 if (RAW) {
                     float n;
                     q = act_rotation(q, n);
