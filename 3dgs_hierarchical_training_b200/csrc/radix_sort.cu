@@ -17,7 +17,13 @@ namespace htgs {
 
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr int SORT_IPT = 16;
+#ifndef HTGS_SORT_IPT
+#define HTGS_SORT_IPT 16
+#endif
+#ifndef HTGS_SORT_MINB
+#define HTGS_SORT_MINB 3
+#endif
+constexpr int SORT_IPT = HTGS_SORT_IPT;
 constexpr int SORT_TILE = SORT_THREADS * SORT_IPT;  // 4096 keys per CTA
 constexpr int SORT_RADIX = 256;
 constexpr int SORT_MAX_PASSES = 8;
@@ -115,7 +121,7 @@ __global__ void __launch_bounds__(SORT_RADIX) sort_scan_hist_kernel(uint32_t* __
     h[threadIdx.x] = e;
 }
 
-__global__ void __launch_bounds__(SORT_THREADS, 3)
+__global__ void __launch_bounds__(SORT_THREADS, HTGS_SORT_MINB)
 onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
                 uint32_t* __restrict__ vout, int64_t n, const uint32_t* __restrict__ n_dev, int shift, int nbits,
                 const uint32_t* __restrict__ digit_start, uint32_t* status, uint32_t* ticket) {
