@@ -229,6 +229,7 @@ class CompactSHGradReducer:
             o += self.P * per
         self.sh_grad = torch.zeros((self.P, self.M, 3), device=device, dtype=torch.float32)
         self._next_local = 0
+        self._side = None  # second stream of the exchange (created on first use)
 
     # -- slots --
     def _slot_offset(self, view):
@@ -288,17 +289,31 @@ class CompactSHGradReducer:
             import htgs_native as nat
             pm, dev, lib = self._peer, self.device, nat.lib()
             with torch.cuda.device(dev):
-                st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+                main = torch.cuda.current_stream(dev)
+                st = ctypes.c_void_p(main.cuda_stream)
                 pm["hdl"].barrier(channel=0)  # every rank's small gradients and slots are complete
+                # The two halves of the exchange touch different data and different resources -- the 11-float all-reduce
+                # is bound by NVLink, the SH rebuild by HBM -- so they run side by side: the rebuild on a second stream,
+                # forked after the barrier and joined before the closing one.
+                if self._side is None:
+                    self._side = torch.cuda.Stream(device=dev)
+                    self._fork, self._join = torch.cuda.Event(), torch.cuda.Event()
+                self._fork.record(main)
+                if self.collective == "multimem":
+                    bases = [self.buf.data_ptr()] * self.world  # pushed: every slot is in the local buffer
+                else:
+                    bases = pm["ptrs"]  # pulled: slot v is read from its owner over NVLink
+                slots = [bases[v // self.views_per_rank] + 4 * self._slot_offset(v) for v in range(self.views_total)]
+                self._side.wait_event(self._fork)
+                with torch.cuda.stream(self._side):
+                    self._expand(slots, means3D, sh_degree)
+                    self._join.record(self._side)
                 if self.collective == "multimem":
                     nat.check(lib.htgs_allreduce_multimem(ctypes.c_void_p(pm["mc"]), self.rank, self.world, self.n_small_pad, st),
                               "htgs_allreduce_multimem")
-                    bases = [self.buf.data_ptr()] * self.world  # pushed: every slot is in the local buffer
                 else:
                     nat.check(lib.htgs_allreduce_p2p(pm["table"], self.rank, self.world, self.n_small_pad, st), "htgs_allreduce_p2p")
-                    bases = pm["ptrs"]  # pulled: slot v is read from its owner over NVLink
-                slots = [bases[v // self.views_per_rank] + 4 * self._slot_offset(v) for v in range(self.views_total)]
-                self._expand(slots, means3D, sh_degree)
+                main.wait_event(self._join)
                 pm["hdl"].barrier(channel=0)  # nobody overwrites a slot / the flat buffer while a peer still reads it
         else:
             if self.world > 1:  # torch.distributed transport (NCCL on GPUs; gloo in the CPU tests of this host logic)
