@@ -94,6 +94,22 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def nvlink_counters(index):
+    """Cumulative NVLink data counters of one GPU (all links summed) from `nvidia-smi nvlink -gt d`, in bytes:
+    (tx, rx), or None when the query is unavailable.  Used at N > 1 to report the link traffic of the timed steps."""
+    import re
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                             text=True, timeout=20).stdout
+    except Exception:
+        return None
+    tx = [int(v) for v in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out)]
+    rx = [int(v) for v in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out)]
+    if not tx or not rx:
+        return None
+    return 1024 * sum(tx), 1024 * sum(rx)
+
+
 def load_plugin():
     pkg = importlib.import_module("3dgs_hierarchical_training_b200")
     pkg.install()
@@ -527,12 +543,22 @@ def run_ours(args, rank, world, local_rank):
     nat.profile_enable(False)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    nvl0 = nvlink_counters(local_rank) if (world > 1 and rank == 0) else None  # outside the timed events, between barriers
+    barrier()
     e0.record()
     for _ in range(args.steps):
         color, radii = step(cam_d, up_d)
     e1.record()
     barrier()
     ms_total = e0.elapsed_time(e1)
+    nvlink = None
+    if nvl0 is not None:
+        nvl1 = nvlink_counters(local_rank)
+        if nvl1 is not None:
+            nvlink = {"tx_bytes_per_step": (nvl1[0] - nvl0[0]) / args.steps, "rx_bytes_per_step": (nvl1[1] - nvl0[1]) / args.steps,
+                      "what": "GPU of rank 0, all links, `nvidia-smi nvlink -gt d` before / after the timed steps (cumulative data "
+                              "counters; the two cross-GPU barriers per step and NCCL's own traffic of the timing barriers are in it)"}
+    barrier()
     # ---- same steps again with the per-stage CUDA-event timers on, for the roofline breakdown only ----
     nat.profile_enable(True)
     ar_timing["on"] = True
@@ -750,6 +776,7 @@ def run_ours(args, rank, world, local_rank):
         out["allreduce_check"] = allreduce_check
         out["allreduce_ms"] = allreduce_ms
         out["exchange_bytes"] = ((44 + 12 * batch_views) if compact else 236) * P
+        out["nvlink"] = nvlink
     if config4 is not None:
         out["config4"] = config4
     # ---- A/B legs against the reference's own CUDA code and the libraries it calls (N = 1 only, after the timed region) ----
