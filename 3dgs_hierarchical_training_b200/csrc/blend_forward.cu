@@ -20,7 +20,10 @@ constexpr int FWD_BATCH = 256;
 // until the pixel saturates), to stats[1] the blended pairs, to stats[2] the pair tests this
 // kernel executes after reach-mask culling.
 // 6 CTAs per SM (40 registers, no spills): 0.514 ms against 0.538 ms at 4 CTAs and 0.525 ms at 8 (config 3)
-constexpr int FWD_MIN_BLOCKS = 6;
+#ifndef HTGS_FWD_MINB
+#define HTGS_FWD_MINB 6
+#endif
+constexpr int FWD_MIN_BLOCKS = HTGS_FWD_MINB;
 template <bool STATS>
 __global__ void __launch_bounds__(HTGS_TILE_PIX, FWD_MIN_BLOCKS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
