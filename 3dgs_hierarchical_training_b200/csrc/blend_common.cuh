@@ -63,19 +63,29 @@ __device__ __forceinline__ void stage_gaussian(StagedGaussian* dst, float2 xy, f
 }
 
 // Minimum over the rectangle dx in [dxl,dxh], dy in [dyl,dyh] of the convex
-// quadratic q = 0.5*(A dx^2 + C dy^2) + B dx dy  ( = -power ).
+// quadratic q = 0.5*(A dx^2 + C dy^2) + B dx dy  ( = -power ), whose unconstrained minimum 0 sits at the origin.
+// Origin inside the rectangle: 0.  Otherwise the minimum lies on the boundary, and only on an edge that FACES the
+// origin: from any point of another edge the straight segment towards the origin runs through the rectangle first (q
+// decreases along it) and leaves through a facing edge.  So at most two edge minimisations are needed -- the nearest
+// vertical edge when the origin is outside the x range, the nearest horizontal edge when it is outside the y range --
+// instead of all four (the staging of a batch, where this runs for every Gaussian and warp block, was 12 % of the
+// forward kernel's instructions with four).
 __device__ __forceinline__ float quad_min_over_rect(float A, float B, float C, float nBiC, float nBiA, float dxl,
                                                     float dxh, float dyl, float dyh) {
-    if (dxl <= 0.f && dxh >= 0.f && dyl <= 0.f && dyh >= 0.f) return 0.f;
+    const bool x_out = dxl > 0.f || dxh < 0.f, y_out = dyl > 0.f || dyh < 0.f;
+    if (!x_out && !y_out) return 0.f;
     float best = 3.0e38f;
-#pragma unroll
-    for (int s = 0; s < 2; s++) {
-        const float ex = s ? dxh : dxl;  // vertical edges dx = ex
+    {
+        const float ex = dxl > 0.f ? dxl : dxh;  // vertical edge nearest to the origin
         const float dy = fminf(dyh, fmaxf(dyl, nBiC * ex));
-        best = fminf(best, 0.5f * (A * ex * ex + C * dy * dy) + B * ex * dy);
-        const float ey = s ? dyh : dyl;  // horizontal edges dy = ey
+        const float v = 0.5f * (A * ex * ex + C * dy * dy) + B * ex * dy;
+        if (x_out) best = v;
+    }
+    {
+        const float ey = dyl > 0.f ? dyl : dyh;  // horizontal edge nearest to the origin
         const float dx = fminf(dxh, fmaxf(dxl, nBiA * ey));
-        best = fminf(best, 0.5f * (A * dx * dx + C * ey * ey) + B * dx * ey);
+        const float v = 0.5f * (A * dx * dx + C * ey * ey) + B * dx * ey;
+        if (y_out) best = fminf(best, v);
     }
     return best;
 }
