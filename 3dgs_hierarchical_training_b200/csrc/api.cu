@@ -52,6 +52,7 @@ BinView bin_view(void* base, int64_t R, int W, int H) {
     b.keys_sorted = carve<uint64_t>(p, n);
     b.keys_alt = carve<uint64_t>(p, n);
     b.values_alt = carve<uint32_t>(p, n);
+    b.reach = carve<uint8_t>(p, n);
     b.sort_scratch = carve<char>(p, sort_scratch_bytes(R));
     b.bytes = (size_t)(p - reinterpret_cast<char*>(base)) + 256;
     return b;
@@ -63,6 +64,7 @@ ImgView img_view(void* base, int W, int H) {
     const size_t tiles = (size_t)((W + HTGS_TILE - 1) / HTGS_TILE) * ((H + HTGS_TILE - 1) / HTGS_TILE);
     v.ranges = carve<uint2>(p, tiles);
     v.n_contrib = carve<uint32_t>(p, (size_t)W * H);
+    v.bin_capacity = carve<uint32_t>(p, 2);
     v.bytes = (size_t)(p - reinterpret_cast<char*>(base)) + 256;
     return v;
 }
@@ -287,7 +289,7 @@ static int forward_render_impl(int P, int64_t R_or_capacity, bool count_on_devic
     if (launch_tile_ranges(R, R_dev, W, H, b.keys_sorted, img.ranges, st)) return 1; }
     { StageTimer t(ST_BLEND_FWD, st);
     if (launch_blend_forward(W, H, img.ranges, b.values_sorted, g, background, out_color, out_depth, out_alpha,
-                             img.n_contrib, st)) return 1; }
+                             img.n_contrib, R > 0 ? b.reach : nullptr, img.bin_capacity, (uint32_t)R, st)) return 1; }
     return 0;
 }
 
@@ -344,7 +346,7 @@ static int backward_impl(const char* who, const float* shs_rest, const float* op
     if (R > 0) {
         StageTimer t(ST_BLEND_BWD, st);
         if (launch_blend_backward(P, W, H, img.ranges, b.values_sorted, g, background, alphas, img.n_contrib, dL_dout_color,
-                                  dL_dout_depth, dL_dout_alpha, gacc, st)) return 1;
+                                  dL_dout_depth, dL_dout_alpha, gacc, b.reach, img.bin_capacity, (uint32_t)R, st)) return 1;
     }
     // compact SH mode: the clamp-masked colour gradient leaves for its view slot as soon as the blend backward is done, on a
     // side stream beside the geometry backward (joined below)

@@ -154,7 +154,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       const float4* __restrict__ conic_opacity, const float4* __restrict__ feat,
                       const float* __restrict__ alphas, const uint32_t* __restrict__ n_contrib,
                       const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth_pix,
-                      const float* __restrict__ dL_dalpha_pix, float* __restrict__ gacc) {
+                      const float* __restrict__ dL_dalpha_pix, float* __restrict__ gacc, const uint8_t* __restrict__ reach,
+                      const uint32_t* __restrict__ bin_capacity, uint32_t capacity) {
     __shared__ WarpPhase s_ph[BLEND_WARPS];                          // 35 072 B
     __shared__ __align__(16) float s_acc[BWD_BATCH][ACC_STRIDE];     //  6 144 B
     __shared__ StagedGaussian s_g[BWD_BATCH];                        //  6 144 B
@@ -173,6 +174,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const int n = (int)(range.y - range.x);
+    // reach masks cached by the forward blend are valid only for the carving they were written under (blend_common.cuh)
+    const bool reach_cached = reach != nullptr && bin_capacity != nullptr && bin_capacity[0] == capacity &&
+                              bin_capacity[1] == REACH_CACHE_MAGIC;
 
     // backward.cu:463-486
     const float T_final = inside ? 1.0f - alphas[pix] : 0.f;
@@ -247,12 +251,15 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         if (top - cnt + 1 >= (int)block_last) continue;  // nothing in this batch was blended by any pixel
         __syncthreads();
         if (tid < cnt) {
-            const uint32_t g = point_list[range.y - 1 - (uint32_t)(base + tid)];  // back to front, backward.cu:502
+            const uint32_t at = range.y - 1 - (uint32_t)(base + tid);  // back to front, backward.cu:502
+            const uint32_t g = point_list[at];
             const float2 xy = means2D[g];
             const float4 co = conic_opacity[g];
             s_id[tid] = g;
             stage_gaussian(&s_g[tid], xy, co, feat[g]);
-            s_mask[tid] = (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
+            // Every list position below the tile's last contributor was staged by the forward, so its mask is in the cache;
+            // positions above it are never live, whatever their (possibly unwritten) mask says.
+            s_mask[tid] = reach_cached ? reach[at] : (uint8_t)block_reach_mask(xy, co, tile_x0, tile_y0);
             float4* a4 = reinterpret_cast<float4*>(&s_acc[tid][0]);
             a4[0] = a4[1] = a4[2] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
@@ -349,11 +356,13 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
 int launch_blend_backward(int P, int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                           const float* bg, const float* alphas, const uint32_t* n_contrib, const float* dL_dpix,
-                          const float* dL_ddepth, const float* dL_dalpha, float* gacc, cudaStream_t st) {
+                          const float* dL_ddepth, const float* dL_dalpha, float* gacc, const uint8_t* reach,
+                          const uint32_t* bin_capacity, uint32_t capacity, cudaStream_t st) {
     (void)P;
     const dim3 grid((W + HTGS_TILE - 1) / HTGS_TILE, (H + HTGS_TILE - 1) / HTGS_TILE);
     blend_backward_kernel<<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, bg, g.means2D, g.conic_opacity, g.feat,
-                                                          alphas, n_contrib, dL_dpix, dL_ddepth, dL_dalpha, gacc);
+                                                          alphas, n_contrib, dL_dpix, dL_ddepth, dL_dalpha, gacc, reach,
+                                                          bin_capacity, capacity);
     HTGS_LAUNCH_CHECK("blend_backward_kernel");
     return 0;
 }

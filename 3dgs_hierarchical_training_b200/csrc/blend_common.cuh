@@ -21,6 +21,12 @@
 namespace htgs {
 
 constexpr int BLEND_WARPS = 8;
+// The forward blend leaves the reach mask of every sorted (tile, Gaussian) instance it staged in the binning buffer, so
+// that the backward need not evaluate it again.  Both sides locate that array by carving the binning buffer with an
+// instance count; the forward records the count it carved with (plus this magic word) in the image buffer, and the
+// backward uses the cached masks only when its own carving count matches -- otherwise (a caller that sized the buffer
+// from a prediction and hands the backward the exact count, a buffer from an older build) it computes the masks itself.
+constexpr uint32_t REACH_CACHE_MAGIC = 0x48544753u;
 
 // pixel block of warp w inside the tile: 2 columns x 4 rows of 8x4 blocks
 __device__ __forceinline__ int warp_block_x(int w) { return (w & 1) * 8; }

@@ -30,11 +30,16 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                      const float4* __restrict__ feat, const float* __restrict__ bg, float* __restrict__ out_color,
                      float* __restrict__ out_depth, float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
-                     unsigned long long* __restrict__ stats) {
+                     unsigned long long* __restrict__ stats, uint8_t* __restrict__ reach, uint32_t* __restrict__ bin_capacity,
+                     uint32_t capacity) {
     __shared__ StagedGaussian s_g[FWD_BATCH];
     __shared__ uint8_t s_mask[FWD_BATCH];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (!STATS && bin_capacity != nullptr && tid == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+        bin_capacity[0] = reach != nullptr ? capacity : 0xffffffffu;  // which carving the cached reach masks belong to
+        bin_capacity[1] = REACH_CACHE_MAGIC;
+    }
     const int tile_x0 = blockIdx.x * HTGS_TILE, tile_y0 = blockIdx.y * HTGS_TILE;
     const int px = tile_x0 + warp_block_x(warp) + (lane & 7);
     const int py = tile_y0 + warp_block_y(warp) + (lane >> 3);
@@ -64,6 +69,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             stage_gaussian(&s_g[tid], xy, co, feat[g]);
             const uint32_t rm = block_reach_mask(xy, co, tile_x0, tile_y0);
             s_mask[tid] = (uint8_t)rm;
+            if (!STATS && reach != nullptr) reach[range.x + base + tid] = (uint8_t)rm;  // kept for the backward
             if (STATS && rm == 0) atomicAdd(&stats[10], 1ull);  // instances whose Gaussian cannot reach any pixel of the tile
         }
         __syncthreads();
@@ -148,11 +154,11 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
 int launch_blend_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                          const float* bg, float* out_color, float* out_depth, float* out_alpha,
-                         uint32_t* n_contrib, cudaStream_t st) {
+                         uint32_t* n_contrib, uint8_t* reach, uint32_t* bin_capacity, uint32_t capacity, cudaStream_t st) {
     const dim3 grid((W + HTGS_TILE - 1) / HTGS_TILE, (H + HTGS_TILE - 1) / HTGS_TILE);
     blend_forward_kernel<false><<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, g.means2D, g.conic_opacity,
                                                                 g.feat, bg, out_color, out_depth, out_alpha, n_contrib,
-                                                                nullptr);
+                                                                nullptr, reach, bin_capacity, capacity);
     HTGS_LAUNCH_CHECK("blend_forward_kernel");
     return 0;
 }
@@ -161,7 +167,7 @@ int launch_blend_stats(int W, int H, const uint2* ranges, const uint32_t* point_
                        unsigned long long* stats, cudaStream_t st) {
     const dim3 grid((W + HTGS_TILE - 1) / HTGS_TILE, (H + HTGS_TILE - 1) / HTGS_TILE);
     blend_forward_kernel<true><<<grid, HTGS_TILE_PIX, 0, st>>>(ranges, point_list, W, H, g.means2D, g.conic_opacity, g.feat,
-                                                               nullptr, nullptr, nullptr, nullptr, nullptr, stats);
+                                                               nullptr, nullptr, nullptr, nullptr, nullptr, stats, nullptr, nullptr, 0u);
     HTGS_LAUNCH_CHECK("blend_forward_kernel<stats>");
     return 0;
 }

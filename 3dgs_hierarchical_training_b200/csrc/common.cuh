@@ -49,12 +49,14 @@ struct BinView {
     uint32_t* values_sorted;
     uint64_t* keys_alt;
     uint32_t* values_alt;
+    uint8_t* reach;  // reach mask of every sorted instance, written by the forward blend for the backward (see blend_common.cuh)
     void* sort_scratch;
     size_t bytes;
 };
 struct ImgView {
     uint2* ranges;
     uint32_t* n_contrib;
+    uint32_t* bin_capacity;  // [2] the instance count the binning buffer of the last forward was carved with, and a magic word
     size_t bytes;
 };
 GeomView geom_view(void* base, int P);
@@ -75,12 +77,13 @@ int launch_tile_ranges(int64_t R, const uint32_t* R_dev, int W, int H, const uin
                        cudaStream_t st);
 int launch_blend_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                          const float* bg, float* out_color, float* out_depth, float* out_alpha,
-                         uint32_t* n_contrib, cudaStream_t st);
+                         uint32_t* n_contrib, uint8_t* reach, uint32_t* bin_capacity, uint32_t capacity, cudaStream_t st);
 int launch_blend_stats(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                        unsigned long long* stats, cudaStream_t st);
 int launch_blend_backward(int P, int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                           const float* bg, const float* alphas, const uint32_t* n_contrib, const float* dL_dpix,
-                          const float* dL_ddepth, const float* dL_dalpha, float* gacc, cudaStream_t st);
+                          const float* dL_ddepth, const float* dL_dalpha, float* gacc, const uint8_t* reach,
+                          const uint32_t* bin_capacity, uint32_t capacity, cudaStream_t st);
 int launch_geom_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
                          const float* shs_rest, const float* opacity_raw, float* dL_dsh_rest, const float* colors_precomp, const float* scales, float scale_modifier,
                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix,

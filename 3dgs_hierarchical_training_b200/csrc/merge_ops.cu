@@ -108,7 +108,7 @@ extern "C" int htgs_importance_accumulate(int P, int D, int M, int64_t R, int W,
     if (R <= 0) return 0;
     // loss = image.sum(): no upstream gradient for depth and alpha (NULL = zero)
     if (launch_blend_backward(P, W, H, img.ranges, b.values_sorted, g, background, alphas, img.n_contrib, dL_dout_color, nullptr,
-                              nullptr, gacc, st)) return 1;
+                              nullptr, gacc, b.reach, img.bin_capacity, (uint32_t)R, st)) return 1;
     importance_accum_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, D, M, means3D, campos, radii, g.clamped, gacc, importance);
     HTGS_LAUNCH_CHECK("importance_accum_kernel");
     return 0;

@@ -81,6 +81,18 @@ def set_sh_compact(provider):
     _SH_COMPACT = provider
 
 
+class _Rendered(int):
+    """`num_rendered` as the reference returns it (an int), carrying the instance count the binning buffer of that
+    forward was CARVED with (the exact R, or the predicted capacity of the speculative path).  The backward hands that
+    count to the C ABI so that both sides see the same layout of the binning buffer -- which is what lets it use the
+    reach masks the forward blend cached there instead of evaluating them again."""
+
+    def __new__(cls, value, carve):
+        obj = super().__new__(cls, value)
+        obj.carve = int(carve)
+        return obj
+
+
 def _pinned_counter(dev):
     t = _PINNED_R.get(dev.index)
     if t is None:
@@ -151,6 +163,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             rendered = ctypes.c_int64(0)
             nat.check(lib.htgs_forward_preprocess(*pre_args, ctypes.byref(rendered), st), "htgs_forward_preprocess")
             R = int(rendered.value)
+            carve = R
             binning = torch.empty(lib.htgs_binning_bytes(R, W, H) if R > 0 else 0, **u8)
             nat.check(lib.htgs_forward_render(P, R, W, H, nat.ptr(background), radii.data_ptr(), geom.data_ptr(),
                                               nat.ptr(binning), *out_args), "htgs_forward_render")
@@ -166,14 +179,16 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                       "htgs_forward_render_capacity")
             counted.synchronize()  # the GPU is already sorting/blending while the host reads R
             R = int(pinned[0]) & 0xFFFFFFFF
+            carve = capacity
             if R > capacity:  # prediction too small: redo phase 2 with the exact size
+                carve = R
                 binning = torch.empty(lib.htgs_binning_bytes(R, W, H), **u8)
                 nat.check(lib.htgs_forward_render(P, R, W, H, nat.ptr(background), radii.data_ptr(), geom.data_ptr(),
                                                   binning.data_ptr(), *out_args), "htgs_forward_render")
         _R_PREDICTION[key] = R
         if debug:
             torch.cuda.synchronize(dev)  # CHECK_CUDA(..., debug) semantics, auxiliary.h:166-173
-    return R, out_color, out_depth, out_alpha, radii, geom, binning, img
+    return _Rendered(R, carve), out_color, out_depth, out_alpha, radii, geom, binning, img
 
 
 def backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
@@ -187,6 +202,8 @@ def backward_impl(background, means3D, radii, colors, scales, rotations, scale_m
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     M = int(sh.size(1)) if sh.numel() != 0 and sh.size(0) != 0 else 0
+    # the count the forward carved the binning buffer with (a plain int from another caller means the exact R)
+    R = getattr(R, "carve", int(R))
     f32 = dict(dtype=torch.float32, device=dev)
     has_sh, has_colors = sh.numel() != 0, colors.numel() != 0
     has_scales, has_cov = scales.numel() != 0, cov3D_precomp.numel() != 0

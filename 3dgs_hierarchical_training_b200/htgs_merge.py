@@ -31,7 +31,7 @@ def accumulate_importance(importance, state, sh_degree, means3D, campos, backgro
     lib = nat.lib()
     with torch.cuda.device(dev):
         scratch = torch.empty(lib.htgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
-        nat.check(lib.htgs_importance_accumulate(P, int(sh_degree), M, int(R), W, H, nat.ptr(background.contiguous()),
+        nat.check(lib.htgs_importance_accumulate(P, int(sh_degree), M, int(getattr(R, "carve", R)), W, H, nat.ptr(background.contiguous()),
                                                  means3D.contiguous().data_ptr(), campos.contiguous().data_ptr(), alpha.data_ptr(),
                                                  radii.data_ptr(), geom.data_ptr(), nat.ptr(binning), img.data_ptr(),
                                                  dL_dcolor.contiguous().data_ptr(), scratch.data_ptr(), importance.data_ptr(),

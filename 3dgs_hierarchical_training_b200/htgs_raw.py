@@ -94,6 +94,7 @@ class _RasterizeRaw(torch.autograd.Function):
             key = (dev.index, P, W, H)
             predicted = _C._R_PREDICTION.get(key) if _C.SPECULATIVE and not rs.debug else None
             R = None
+            carve = None  # the instance count the binning buffer ends up carved with (see _C._Rendered)
             if predicted is not None:
                 capacity = int(predicted * _C.CAPACITY_MARGIN) + 8192
                 binning = torch.empty(lib.htgs_binning_bytes(capacity, W, H), **u8)
@@ -101,9 +102,11 @@ class _RasterizeRaw(torch.autograd.Function):
                                                            binning.data_ptr(), *out_args), "htgs_forward_render_capacity")
                 counted.synchronize()
                 R = int(pinned[0]) & 0xFFFFFFFF
+                carve = capacity
             if predicted is None or R > capacity:
                 counted.synchronize()
                 R = int(pinned[0]) & 0xFFFFFFFF
+                carve = R
                 binning = torch.empty(lib.htgs_binning_bytes(R, W, H) if R > 0 else 0, **u8)
                 nat.check(lib.htgs_forward_render(P, R, W, H, bg.data_ptr(), radii.data_ptr(), geom.data_ptr(),
                                                   nat.ptr(binning), *out_args), "htgs_forward_render")
@@ -111,7 +114,7 @@ class _RasterizeRaw(torch.autograd.Function):
             if rs.debug:
                 torch.cuda.synchronize(dev)
         ctx.raster_settings = rs
-        ctx.num_rendered = R
+        ctx.num_rendered = _C._Rendered(R, carve)
         ctx.save_for_backward(xyz, opacity_raw, features_dc, features_rest, scaling_raw, rotation_raw, radii, geom, binning,
                               img, alpha)
         ctx.mark_non_differentiable(radii)
@@ -140,7 +143,7 @@ class _RasterizeRaw(torch.autograd.Function):
             drot = _grad_buffer("rotations", (P, 4), True, **f32)
             scratch = torch.empty(lib.htgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
             nat.check(lib.htgs_backward_raw(
-                P, int(rs.sh_degree), int(ctx.num_rendered), W, H, bg.data_ptr(), xyz.data_ptr(), features_dc.data_ptr(),
+                P, int(rs.sh_degree), int(ctx.num_rendered.carve), W, H, bg.data_ptr(), xyz.data_ptr(), features_dc.data_ptr(),
                 features_rest.data_ptr(), alpha.data_ptr(), scaling_raw.data_ptr(), float(rs.scale_modifier),
                 rotation_raw.data_ptr(), opacity_raw.data_ptr(), view.data_ptr(), proj.data_ptr(), campos.data_ptr(),
                 float(rs.tanfovx), float(rs.tanfovy), radii.data_ptr(), geom.data_ptr(), nat.ptr(binning), img.data_ptr(),

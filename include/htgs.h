@@ -146,7 +146,11 @@ int htgs_forward_render_capacity(int P, int64_t capacity, int W, int H, const fl
  *   dL_dcolors[P,3]   when colors_precomp != NULL (else may be NULL)
  *   dL_dsh[P,M,3]     when shs != NULL
  *   dL_dscales[P,3], dL_drotations[P,4]  when scales != NULL
- *   dL_dcov3D[P,6]    when cov3D_precomp != NULL (else may be NULL)          */
+ *   dL_dcov3D[P,6]    when cov3D_precomp != NULL (else may be NULL)
+ * R: pass the instance count the forward's binning buffer was SIZED with -- the R of htgs_forward_render, or the
+ * capacity of htgs_forward_render_capacity.  The forward blend leaves the per-instance reach masks in that buffer and
+ * records the count it carved the buffer with; when the backward's count matches it reuses them, otherwise (e.g. the
+ * exact R after a capacity-sized forward) it recomputes them: same result, slightly slower.                        */
 int htgs_backward(int P, int D, int M, int64_t R, int W, int H, const float* background,
                   const float* means3D, const float* shs, const float* colors_precomp,
                   const float* alphas, const float* scales, float scale_modifier,

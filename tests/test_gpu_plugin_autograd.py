@@ -7,6 +7,7 @@ import torch
 
 import htgs_synthetic as syn
 from helpers import GRAD_RTOL, np_, rel_inf, run_ours
+import htgs_native as nat
 from oracle import golden
 
 pytestmark = pytest.mark.gpu
@@ -187,3 +188,35 @@ def test_speculative_forward_reruns_when_the_predicted_capacity_is_too_small():
     finally:
         _C.SPECULATIVE = saved
         _C._R_PREDICTION.pop(key, None)
+
+
+def test_backward_reuses_cached_reach_masks_only_under_the_forwards_carving():
+    """The forward blend caches the per-instance reach masks in the binning buffer; the backward may use them only when
+    it carves that buffer with the count the forward used (`num_rendered.carve`).  Handing it the exact R after a
+    capacity-sized (speculative) forward must silently fall back to recomputing them: same gradients either way."""
+    from diff_gaussian_rasterization import _C
+    cfg, scene, cam, up = syn.make_config("config1", device="cuda")
+    bg = torch.tensor([0.1, 0.2, 0.3], device="cuda")
+    empty = torch.Tensor([])
+    args = (bg, scene["means3D"], empty, scene["opacities"], scene["scales"], scene["rotations"], 1.0, empty, cam["viewmatrix"],
+            cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], cfg["H"], cfg["W"], scene["shs"], 3, cam["campos"], False, False)
+    _C.rasterize_gaussians(*args)            # first call: exact two-phase flow, seeds the prediction
+    R, color, depth, alpha, radii, geom, binning, img = _C.rasterize_gaussians(*args)   # speculative: capacity-sized buffer
+    assert isinstance(R, int) and R.carve > int(R)
+
+    def bwd(count):
+        g = _C.rasterize_gaussians_backward(bg, scene["means3D"], radii, empty, scene["scales"], scene["rotations"], 1.0, empty,
+                                            cam["viewmatrix"], cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], up["dL_dcolor"],
+                                            up["dL_ddepth"], up["dL_dalpha"], scene["shs"], 3, cam["campos"], geom, count, binning, img,
+                                            alpha, False)
+        torch.cuda.synchronize()
+        return g
+
+    cached, recomputed = bwd(R), bwd(int(R))
+    for a, b in zip(cached, recomputed):
+        assert rel_inf(a, b) <= GRAD_RTOL
+    # and a cache written under another carving is not trusted: poison it, the fallback must not read it
+    lay = nat.binning_layout(int(R), cfg["W"], cfg["H"])
+    binning[lay["values_alt"] + 4 * int(R):lay["sort_scratch"]] = 0   # where the exact-R carving would look for masks
+    for a, b in zip(bwd(int(R)), cached):
+        assert rel_inf(a, b) <= GRAD_RTOL
