@@ -76,52 +76,38 @@ make_keys_kernel(int P, int gx, int gy, const int* __restrict__ radii, const flo
     }
 }
 
-// One WARP per tile: lower bound of (tile << 32) in the sorted keys gives the range start, lower bound of
-// ((tile+1) << 32) its end.  Tiles with no instances get (0,0) like the reference's memset.
-// The kernel is a chain of dependent L2 round trips, so the search is 32-ary: every step the 32 lanes probe 32 evenly
-// spaced keys of the remaining interval for both bounds at once and a ballot picks the sub-interval -- 5 steps for
-// 3.4 M keys instead of the 22 of a binary search (round 1 ran two 4-ary searches per THREAD, 11 steps).  Measured:
-// 12.7 -> 8.6 us at config 5 (1024 tiles), unchanged 12.8 us at config 3 (8160 tiles, where the probes of neighbouring
-// tiles stop sharing cache lines early).
+// One WARP per tile BOUNDARY: b(t) = first index whose key carries a tile id >= t, for t = 0 .. tiles.  Tile t owns
+// [b(t), b(t+1)), so warp t writes ranges[t].x and ranges[t-1].y; tiles with no instances get (0,0) like the
+// reference's memset (the warp sees that from the keys on either side of its boundary).
+// The search is 32-ary: every step the 32 lanes probe 32 evenly spaced keys of the remaining interval and a ballot
+// picks the sub-interval -- 5-7 steps for 3.4 M keys instead of the 22 of a binary search.  Only the high word of a
+// key (the tile id) is read and compared, all index arithmetic is 32-bit.  ncu (config 3): the two-bounds-per-warp
+// 64-bit version of this kernel executed 665 instructions per warp and was ISSUE-bound at 11.3 us, not latency-bound.
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(int64_t R, const uint32_t* __restrict__ R_dev, int tiles, const uint64_t* __restrict__ keys,
+tile_ranges_kernel(uint32_t R, const uint32_t* __restrict__ R_dev, int tiles, const uint64_t* __restrict__ keys,
                    uint2* __restrict__ ranges) {
     const int t = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
-    const int lane = threadIdx.x & 31;
-    if (t >= tiles) return;
-    if (R_dev) R = min(R, (int64_t)*R_dev);
-    const uint64_t target[2] = {(uint64_t)t << 32, (uint64_t)(t + 1) << 32};
-    int64_t lo[2] = {0, 0}, hi[2] = {R, R};  // the first index with key >= target lies in [lo, hi]
-    while (lo[0] < hi[0] || lo[1] < hi[1]) {
-        int64_t at[2], step[2];
-        bool ge[2];
-#pragma unroll
-        for (int s = 0; s < 2; s++) {
-            step[s] = (hi[s] - lo[s] + 31) >> 5;  // >= 1 while the interval is not empty
-            at[s] = lo[s] + (int64_t)lane * step[s];
-            ge[s] = true;                         // probes past the interval count as "key >= target"
-        }
-        uint64_t k[2] = {0, 0};
-#pragma unroll
-        for (int s = 0; s < 2; s++)
-            if (lo[s] < hi[s] && at[s] < hi[s]) k[s] = __ldg(keys + at[s]);
-#pragma unroll
-        for (int s = 0; s < 2; s++) {
-            if (lo[s] < hi[s]) {
-                if (at[s] < hi[s]) ge[s] = k[s] >= target[s];
-                const uint32_t m = __ballot_sync(0xffffffffu, ge[s]);
-                const int f = m ? __ffs(m) - 1 : 32;  // first probe with key >= target (32: none)
-                // keys at probes < f are below the target, the key at probe f is not: the bound lies in (probe f-1, probe f]
-                const int64_t nlo = f == 0 ? lo[s] : lo[s] + (int64_t)(f - 1) * step[s] + 1;
-                const int64_t nhi = f == 32 ? hi[s] : min(hi[s], lo[s] + (int64_t)f * step[s]);
-                lo[s] = nlo;
-                hi[s] = nhi;
-            } else {
-                (void)__ballot_sync(0xffffffffu, false);
-            }
-        }
+    const uint32_t lane = threadIdx.x & 31;
+    if (t > tiles) return;
+    if (R_dev) R = min(R, *R_dev);
+    const uint32_t* tile_of = reinterpret_cast<const uint32_t*>(keys) + 1;  // tile id of key i: tile_of[2 * i]
+    uint32_t lo = 0, hi = R;  // the boundary lies in [lo, hi]
+    while (lo < hi) {
+        const uint32_t step = (hi - lo + 31) >> 5;  // >= 1
+        const uint32_t at = lo + lane * step;  // R < 2^30 (checked at the C ABI): no overflow, 2 * at fits too
+        bool ge = true;                             // probes past the interval count as "tile id >= t"
+        if (at < hi) ge = __ldg(tile_of + 2 * at) >= (uint32_t)t;
+        const uint32_t m = __ballot_sync(0xffffffffu, ge);
+        const uint32_t f = m ? (uint32_t)__ffs(m) - 1 : 32;  // first such probe (32: none)
+        // probes below f are under the boundary, probe f is not: the boundary lies in (probe f-1, probe f]
+        const uint32_t nlo = f == 0 ? lo : lo + (f - 1) * step + 1;
+        const uint32_t nhi = f == 32 ? hi : min(hi, lo + f * step);
+        lo = nlo;
+        hi = nhi;
     }
-    if (lane == 0) ranges[t] = lo[0] == lo[1] ? make_uint2(0, 0) : make_uint2((uint32_t)lo[0], (uint32_t)lo[1]);
+    uint32_t* out = reinterpret_cast<uint32_t*>(ranges);
+    if (lane == 0 && t < tiles) out[2 * t] = (lo < R && __ldg(tile_of + 2 * lo) == (uint32_t)t) ? lo : 0;
+    if (lane == 1 && t > 0) out[2 * t - 1] = (lo > 0 && __ldg(tile_of + 2 * (lo - 1)) == (uint32_t)(t - 1)) ? lo : 0;
 }
 
 int launch_make_keys(int P, int W, int H, const int* radii, const GeomView& g, uint64_t* keys, uint32_t* values,
@@ -138,7 +124,7 @@ int launch_tile_ranges(int64_t R, const uint32_t* R_dev, int W, int H, const uin
                        cudaStream_t st) {
     const int gx = (W + HTGS_TILE - 1) / HTGS_TILE, gy = (H + HTGS_TILE - 1) / HTGS_TILE;
     const int tiles = gx * gy;
-    tile_ranges_kernel<<<(tiles + 7) / 8, 256, 0, st>>>(R, R_dev, tiles, keys_sorted, ranges);
+    tile_ranges_kernel<<<(tiles + 1 + 7) / 8, 256, 0, st>>>((uint32_t)R, R_dev, tiles, keys_sorted, ranges);
     HTGS_LAUNCH_CHECK("tile_ranges_kernel");
     return 0;
 }
