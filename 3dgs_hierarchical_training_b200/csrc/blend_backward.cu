@@ -280,14 +280,13 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
                 const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
-                const float4 q0 = lds128(a);       // mean.xy, conic.x, conic.z
-                const float4 q1 = lds128(a + 16);  // conic.y, opacity, r, g
+                const float4 q0 = lds128(a);       // mean.xy, conic.y, conic.z
+                const float4 q1 = lds128(a + 16);  // conic.x, opacity, r, g
                 const uint64_t dxy = sub2(pk2(q0.x, q0.y), pxy);   // (dx, dy)
-                float dx, dy, tx, ty, my, mc;
+                float dx, dy, my, mc;
                 up2(dxy, dx, dy);
-                up2(mul2(dxy, pk2(q0.z, q0.w)), tx, ty);                  // (dx*cx, dy*cz)
-                up2(mul2(pk2(dy, dy), pk2(ty, MU(dx, q1.x))), my, mc);    // (dy*(dy*cz), dy*(dx*cy))
-                const float power = FM(FM(dx, tx, my), -0.5f, -mc);       // pair_power()
+                up2(mul2(pk2(dy, dy), mul2(dxy, pk2(q0.z, q0.w))), mc, my);  // (dy*(dx*cy), dy*(dy*cz))
+                const float power = FM(FM(dx, MU(dx, q1.x), my), -0.5f, -mc);  // pair_power()
                 const float G = expf(power);
                 const float alpha = fminf(0.99f, MU(q1.y, G));
                 // `contributor` after its decrement is chunk_top - b (backward.cu:517-519)
@@ -343,7 +342,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const float s5 = fmaf(X, s2, fmaf(-Y, Sx, Sxy));                    // sum w dx dy
             const float s6 = fmaf(Y, s2 - Sy, Syy);                             // sum w dy dy
             // moments -> gradients (backward.cu:582-598), per-Gaussian constants applied once here
-            const float cx = q0.z, cz = q0.w, cy = q1.x, op = q1.y;
+            const float cy = q0.z, cz = q0.w, cx = q1.x, op = q1.y;
             const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:490-491
             const float gmx = -op * (cx * s1 + cy * s2) * ddelx_dx;
             const float gmy = -op * (cz * s2 + cy * s1) * ddely_dy;

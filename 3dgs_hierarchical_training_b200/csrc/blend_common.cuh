@@ -33,8 +33,9 @@ __device__ __forceinline__ int warp_block_x(int w) { return (w & 1) * 8; }
 __device__ __forceinline__ int warp_block_y(int w) { return (w >> 1) * 4; }
 
 // One staged Gaussian in shared memory (48 B, 16-byte aligned):
-//   q0 = (mean.x, mean.y, conic.x, conic.z)   q1 = (conic.y, opacity, r, g)   q2 = (b, depth, -, -)
-// conic.x and conic.z sit next to each other so that (dx*cx, dy*cz) is one packed multiply (below).
+//   q0 = (mean.x, mean.y, conic.y, conic.z)   q1 = (conic.x, opacity, r, g)   q2 = (b, depth, -, -)
+// conic.y and conic.z sit next to each other so that (dx*cy, dy*cz) is one packed multiply and dy * that pair the
+// next one: the exponent costs FADD2, FMUL2, FMUL, FMUL2, FFMA, FFMA with no register move to form a pair.
 struct __align__(16) StagedGaussian {
     float4 q0, q1, q2;
 };
@@ -63,8 +64,8 @@ __device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) { uint64_t d; a
 __device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) { uint64_t d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 
 __device__ __forceinline__ void stage_gaussian(StagedGaussian* dst, float2 xy, float4 co, float4 f) {
-    dst->q0 = make_float4(xy.x, xy.y, co.x, co.z);
-    dst->q1 = make_float4(co.y, co.w, f.x, f.y);
+    dst->q0 = make_float4(xy.x, xy.y, co.y, co.z);
+    dst->q1 = make_float4(co.x, co.w, f.x, f.y);
     dst->q2 = make_float4(f.z, f.w, 0.f, 0.f);
 }
 

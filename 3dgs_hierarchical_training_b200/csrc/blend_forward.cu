@@ -45,22 +45,28 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     const int py = tile_y0 + warp_block_y(warp) + (lane >> 3);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
-    int done = inside ? 0 : 1;
+    // A saturated pixel (forward.cu:351-355 `done`) is marked by a NEGATIVE transmittance: its test_T = T * (1 - alpha)
+    // is then negative, hence below the 1e-4 threshold, and the pair is rejected by the comparison that is evaluated
+    // anyway -- no separate flag to test and to set in every visit.  |T| is the value the reference keeps.
+#define HTGS_DONE (T < 0.f)
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const int n = (int)(range.y - range.x);
     const uint32_t sg_base = smem_u32(s_g);
 
-    float T = 1.0f, wsum = 0.f;
-    uint64_t C01 = pk2(0.f, 0.f), C2d = pk2(0.f, 0.f);  // (C0, C1) and (C2, depth sum) as packed pairs
+    float T = inside ? 1.0f : -1.0f, wsum = 0.f;
+    // Scalar accumulators on purpose: ptxas if-converts the short blend block below, and a predicated packed FFMA2 then
+    // lands in a temporary pair that two moves copy back; predicated scalar FFMAs accumulate in place.
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f, dsum = 0.f;
     const uint64_t pxy = pk2(pxf, pyf);
     uint32_t last_contributor = 0;
+    int last_in_batch = -1;  // batch position of the last pair this pixel blended in the current batch (-1: none)
     uint32_t st_blended = 0, st_tested = 0, st_done_pos = 0;
     uint32_t st_hist[7] = {0, 0, 0, 0, 0, 0, 0};  // warp visits by number of blending lanes: 0, 1, 2-4, 5-8, 9-16, 17-24, 25-32
 
     for (int base = 0; base < n; base += FWD_BATCH) {
         // leave when every pixel of the tile is saturated (forward.cu:313-315)
-        if (__syncthreads_count(done) == HTGS_TILE_PIX) break;
+        if (__syncthreads_count(HTGS_DONE) == HTGS_TILE_PIX) break;
         const int cnt = min(FWD_BATCH, n - base);
         if (tid < cnt) {
             const uint32_t g = point_list[range.x + base + tid];
@@ -73,56 +79,60 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
             if (STATS && rm == 0) atomicAdd(&stats[10], 1ull);  // instances whose Gaussian cannot reach any pixel of the tile
         }
         __syncthreads();
-        if (__all_sync(0xffffffffu, done)) continue;
+        if (__all_sync(0xffffffffu, HTGS_DONE)) continue;
         for (int c0 = 0; c0 < cnt; c0 += 32) {
             const int j = c0 + lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1);
             uint32_t m = __ballot_sync(0xffffffffu, mine);
             const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
-            const uint32_t chunk_pos = (uint32_t)(base + c0 + 1);
             while (m) {
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
                 const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
-                const float4 q0 = lds128(a);       // mean.xy, conic.x, conic.z
-                const float4 q1 = lds128(a + 16);  // conic.y, opacity, r, g
+                const float4 q0 = lds128(a);       // mean.xy, conic.y, conic.z
+                const float4 q1 = lds128(a + 16);  // conic.x, opacity, r, g
                 const uint64_t d2 = sub2(pk2(q0.x, q0.y), pxy);     // (dx, dy)
-                const uint64_t t2 = mul2(d2, pk2(q0.z, q0.w));      // (dx*cx, dy*cz)
-                float dx, dy, tx, ty;
+                float dx, dy, my, mc;
                 up2(d2, dx, dy);
-                up2(t2, tx, ty);
                 // pair_power(): fma(fma(dx, dx*cx, dy*(dy*cz)), -0.5, -(dy*(dx*cy)))
-                float my, mc;
-                up2(mul2(pk2(dy, dy), pk2(ty, MU(dx, q1.x))), my, mc);  // (dy*(dy*cz), dy*(dx*cy))
-                const float power = FM(FM(dx, tx, my), -0.5f, -mc);
+                up2(mul2(pk2(dy, dy), mul2(d2, pk2(q0.z, q0.w))), mc, my);  // (dy*(dx*cy), dy*(dy*cz))
+                const float power = FM(FM(dx, MU(dx, q1.x), my), -0.5f, -mc);
                 const float alpha = fminf(0.99f, MU(q1.y, expf(power)));
                 const float test_T = MU(T, SB(1.0f, alpha));
                 // the reference's three rejections (forward.cu:340-355) as one predicate chain
-                const bool live = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                if (STATS) st_tested += done ? 0u : 1u;
-                const bool kill = live && (test_T < 0.0001f);
-                if (kill) {
-                    done = 1;
-                    if (STATS) st_done_pos = chunk_pos + (uint32_t)b;
-                }
+                const bool live = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (STATS) st_tested += HTGS_DONE ? 0u : 1u;
+                const bool kill = live && (test_T < 0.0001f);  // also true again for a pixel that is already saturated
+                if (STATS && kill && !HTGS_DONE) st_done_pos = (uint32_t)(base + c0 + b + 1);
                 if (STATS) {
                     const int nl = __popc(__ballot_sync(0xffffffffu, live && !kill));
                     const int bucket = nl == 0 ? 0 : nl == 1 ? 1 : nl <= 4 ? 2 : nl <= 8 ? 3 : nl <= 16 ? 4 : nl <= 24 ? 5 : 6;
 #pragma unroll
                     for (int k = 0; k < 7; k++) st_hist[k] += (k == bucket) ? 1u : 0u;
                 }
-                if (live && !kill) {
+                const bool blend = live && !(test_T < 0.0001f);
+                if (kill) T = -fabsf(T);
+                if (blend) {
                     const float2 q2 = lds64(a + 32);  // b, depth
-                    const uint64_t aa = pk2(alpha, alpha), TT = pk2(T, T);
-                    C01 = fma2(TT, mul2(aa, pk2(q1.z, q1.w)), C01);  // C += T * (alpha * c), forward.cu:359-361
-                    C2d = fma2(TT, mul2(aa, pk2(q2.x, q2.y)), C2d);
+                    const uint64_t aa = pk2(alpha, alpha);
+                    float ac0, ac1, ac2, ad;
+                    up2(mul2(aa, pk2(q1.z, q1.w)), ac0, ac1);  // alpha * c, forward.cu:359-361
+                    up2(mul2(aa, pk2(q2.x, q2.y)), ac2, ad);
+                    C0 = FM(T, ac0, C0);                       // C += T * (alpha * c)
+                    C1 = FM(T, ac1, C1);
+                    C2 = FM(T, ac2, C2);
+                    dsum = FM(T, ad, dsum);
                     wsum = FM(T, alpha, wsum);
                     T = test_T;
-                    last_contributor = chunk_pos + (uint32_t)b;
+                    last_in_batch = c0 + b;
                     if (STATS) st_blended++;
                 }
             }
-            if (__all_sync(0xffffffffu, done)) break;
+            if (__all_sync(0xffffffffu, HTGS_DONE)) break;
+        }
+        if (last_in_batch >= 0) {  // forward.cu:365: position in the tile's list, counted from 1
+            last_contributor = (uint32_t)(base + last_in_batch + 1);
+            last_in_batch = -1;
         }
     }
     if (STATS) {
@@ -137,9 +147,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         }
         return;
     }
-    float C0, C1, C2, dsum;
-    up2(C01, C0, C1);
-    up2(C2d, C2, dsum);
+    T = fabsf(T);
+#undef HTGS_DONE
     if (inside) {
         const size_t pix = (size_t)py * W + px;
         const size_t plane = (size_t)H * W;
