@@ -200,7 +200,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     // reference folds the previous Gaussian's colour in lazily (backward.cu:547-567, last_alpha / last_color carried to
     // the next iteration); folding it in right after use is the same fma on the same values and carries one float
     // instead of four
-    float A = 0.f;
+    // The alpha channel's "colour" is the constant 1, so its term da enters Cd - A only as a constant: it is folded into
+    // the start value (A' = A - da obeys the same recurrence), which keeps da out of the per-visit sum.
+    float A = -da;
 
     // This pixel's column of the A operand, scattered into fragment order: pixel p = lane sits in k-step (p & 7) >> 1,
     // fragment lanes g*4 + (p >> 3) for every row pair (g, g+8), element (p & 1) of the k-step's pixel pair.
@@ -239,7 +241,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 #pragma unroll
     for (int w = 0; w < BLEND_WARPS; w++) block_last = max(block_last, s_warp_last[w]);
 
-    const uint64_t pxy = pk2(pxf, pyf), d0_d1 = pk2(d0, d1), d2_dd = pk2(d2, dd), da_0 = pk2(da, 0.f);
+    const uint64_t pxy = pk2(pxf, pyf), d0_d1 = pk2(d0, d1), d2_dd = pk2(d2, dd);
     // (the bases pass through an opaque asm so that ptxas keeps them in registers: it otherwise rebuilds the shared
     // window address -- S2UR CgaCtaId, UMOV, UIADD3, ULEA -- inside every visit)
     uint32_t sg_base, acc_base;
@@ -251,6 +253,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const int cnt = min(BWD_BATCH, n - base);
         // list positions (0-based, front to back) covered by this batch: top .. top-cnt+1
         const int top = n - 1 - base;
+        const int jmin = top - (int)last_contributor + 1;  // first batch position this pixel's blend reached (may be < 0)
         if (top - cnt + 1 >= (int)block_last) continue;  // nothing in this batch was blended by any pixel
         __syncthreads();
         if (tid < cnt) {
@@ -275,7 +278,6 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1) && (uint32_t)(top - j) < warp_last;
             uint32_t m = __ballot_sync(0xffffffffu, mine);
             const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
-            const uint32_t chunk_top = (uint32_t)(top - c0);
             while (m) {
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
@@ -289,30 +291,32 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const float power = FM(FM(dx, MU(dx, q1.x), my), -0.5f, -mc);  // pair_power()
                 const float G = expf(power);
                 const float alpha = fminf(0.99f, MU(q1.y, G));
-                // `contributor` after its decrement is chunk_top - b (backward.cu:517-519)
-                const bool live = (chunk_top - (uint32_t)b) < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                // `contributor` after its decrement is top - (c0 + b) (backward.cu:517-519); it is below this pixel's last
+                // contributor from batch position jmin on
+                const bool live = (c0 + b) >= jmin && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 // Everything a lane contributes is proportional to w = G*dL/dalpha or to aT = alpha*T; lanes that do
-                // not blend this Gaussian park zeros.
-                float w = 0.f, aT = 0.f;
-                if (live) {
-                    const float2 q2 = lds64(a + 32);  // b, depth
-                    // T = T / (1 - alpha), backward.cu:534.  One Newton step on the hardware reciprocal
-                    // (<= 1 ulp from div.rn, 4 issue slots instead of 10); also feeds the background term.
-                    const float one_m_a = SB(1.f, alpha);
-                    float rinv;
-                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(one_m_a));
-                    rinv = fmaf(fmaf(-one_m_a, rinv, 1.f), rinv, rinv);
-                    T = T * rinv;
-                    aT = alpha * T;
-                    // Cd = r*d0 + g*d1 + b*d2 + depth*dd + da as two packed chains
-                    float c_lo, c_hi;
-                    up2(fma2(pk2(q2.x, q2.y), d2_dd, fma2(pk2(q1.z, q1.w), d0_d1, da_0)), c_lo, c_hi);
-                    const float Cd = c_lo + c_hi;
-                    float dL_dopa = (Cd - A) * T;
-                    A = fmaf(alpha, Cd, one_m_a * A);
-                    if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
-                    w = G * dL_dopa;
-                }
+                // not blend this Gaussian park zeros.  Straight-line code with selects at the end: a warp visit without
+                // any live lane is rare (3 % at config 3), and the branch around an 18-instruction block cost a
+                // BSSY/BRA/BSYNC triple plus the zero defaults in every visit.
+                const float2 q2 = lds64(a + 32);  // b, depth
+                // T = T / (1 - alpha), backward.cu:534.  One Newton step on the hardware reciprocal
+                // (<= 1 ulp from div.rn, 4 issue slots instead of 10); also feeds the background term.
+                const float one_m_a = SB(1.f, alpha);
+                float rinv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(one_m_a));
+                rinv = fmaf(fmaf(-one_m_a, rinv, 1.f), rinv, rinv);
+                const float Tn = T * rinv;
+                // Cd = r*d0 + g*d1 + b*d2 + depth*dd as two packed chains (da: see A)
+                float c_lo, c_hi;
+                up2(fma2(pk2(q2.x, q2.y), d2_dd, mul2(pk2(q1.z, q1.w), d0_d1)), c_lo, c_hi);
+                const float Cd = c_lo + c_hi;
+                float dL_dopa = (Cd - A) * Tn;
+                const float An = fmaf(alpha, Cd, one_m_a * A);
+                if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
+                const float w = live ? G * dL_dopa : 0.f;
+                const float aT = live ? alpha * Tn : 0.f;
+                T = live ? Tn : T;
+                A = live ? An : A;
                 if (__any_sync(0xffffffffu, live)) {
                     sts32(park_at, w);
                     sts32(park_at + (uint32_t)(PH_ROW_AT * PH_STRIDE * 4), aT);
