@@ -274,14 +274,21 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         uint64_t slots = 0;       // their batch indices, one byte each, newest in the lowest byte (warp-uniform)
         uint32_t park_at = park;  // where this lane parks the next visit
         for (int c0 = 0; c0 < cnt; c0 += 32) {
-            const int j = c0 + lane;
+            // lane L tests batch position c0 + 31 - L: the LEADING one of the ballot is the next position to visit (see the
+            // forward kernel)
+            const int j = c0 + 31 - lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1) && (uint32_t)(top - j) < warp_last;
             uint32_t m = __ballot_sync(0xffffffffu, mine);
-            const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
+            const int c31 = c0 + 31;
+            const uint32_t chunk_end = sg_base + (uint32_t)c31 * STAGED_BYTES;
+            const int pmax = c31 - jmin;  // this pixel blended the positions with bit index <= pmax
             while (m) {
-                const int b = __ffs(m) - 1;
-                m &= m - 1;
-                const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
+                int p;
+                uint32_t below;
+                asm("bfind.u32 %0, %1;" : "=r"(p) : "r"(m));
+                asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(below) : "r"(p));
+                m &= below;
+                const uint32_t a = chunk_end - (uint32_t)p * STAGED_BYTES;
                 const float4 q0 = lds128(a);       // mean.xy, conic.y, conic.z
                 const float4 q1 = lds128(a + 16);  // conic.x, opacity, r, g
                 const uint64_t dxy = sub2(pk2(q0.x, q0.y), pxy);   // (dx, dy)
@@ -293,7 +300,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const float alpha = fminf(0.99f, MU(q1.y, G));
                 // `contributor` after its decrement is top - (c0 + b) (backward.cu:517-519); it is below this pixel's last
                 // contributor from batch position jmin on
-                const bool live = (c0 + b) >= jmin && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                const bool live = p <= pmax && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 // Everything a lane contributes is proportional to w = G*dL/dalpha or to aT = alpha*T; lanes that do
                 // not blend this Gaussian park zeros.  Straight-line code with selects at the end: a warp visit without
                 // any live lane is rare (3 % at config 3), and the branch around an 18-instruction block cost a
@@ -320,7 +327,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 if (__any_sync(0xffffffffu, live)) {
                     sts32(park_at, w);
                     sts32(park_at + (uint32_t)(PH_ROW_AT * PH_STRIDE * 4), aT);
-                    slots = (slots << 8) | (uint64_t)(uint32_t)(c0 + b);
+                    slots = (slots << 8) | (uint64_t)(uint32_t)(c31 - p);
                     park_at += (uint32_t)(PH_STRIDE * 4);
                     if (++parked == PH_N) {
                         reduce_phase(ph, acc_base, PH_N, lane, slots);

@@ -81,14 +81,20 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         __syncthreads();
         if (__all_sync(0xffffffffu, HTGS_DONE)) continue;
         for (int c0 = 0; c0 < cnt; c0 += 32) {
-            const int j = c0 + lane;
+            // Lane L tests batch position c0 + 31 - L: the LEADING one of the ballot is then the next position to visit, and
+            // the loop works on its bit index p directly (FLO, IMAD for the address) instead of BREV, FLO, ADD, IMAD.
+            const int j = c0 + 31 - lane;
             const bool mine = j < cnt && ((s_mask[j] >> warp) & 1);
             uint32_t m = __ballot_sync(0xffffffffu, mine);
-            const uint32_t chunk_addr = sg_base + (uint32_t)c0 * STAGED_BYTES;
+            const int c31 = c0 + 31;
+            const uint32_t chunk_end = sg_base + (uint32_t)c31 * STAGED_BYTES;
             while (m) {
-                const int b = __ffs(m) - 1;
-                m &= m - 1;
-                const uint32_t a = chunk_addr + (uint32_t)b * STAGED_BYTES;
+                int p;  // index of the leading one (bfind -> one FLO; written as 31 - __clz(m) nvcc rebuilds clz and undoes the saving)
+                asm("bfind.u32 %0, %1;" : "=r"(p) : "r"(m));
+                uint32_t below;  // the p bits under the leading one
+                asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(below) : "r"(p));
+                m &= below;
+                const uint32_t a = chunk_end - (uint32_t)p * STAGED_BYTES;
                 const float4 q0 = lds128(a);       // mean.xy, conic.y, conic.z
                 const float4 q1 = lds128(a + 16);  // conic.x, opacity, r, g
                 const uint64_t d2 = sub2(pk2(q0.x, q0.y), pxy);     // (dx, dy)
@@ -103,7 +109,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 const bool live = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 if (STATS) st_tested += HTGS_DONE ? 0u : 1u;
                 const bool kill = live && (test_T < 0.0001f);  // also true again for a pixel that is already saturated
-                if (STATS && kill && !HTGS_DONE) st_done_pos = (uint32_t)(base + c0 + b + 1);
+                if (STATS && kill && !HTGS_DONE) st_done_pos = (uint32_t)(base + c31 - p + 1);
                 if (STATS) {
                     const int nl = __popc(__ballot_sync(0xffffffffu, live && !kill));
                     const int bucket = nl == 0 ? 0 : nl == 1 ? 1 : nl <= 4 ? 2 : nl <= 8 ? 3 : nl <= 16 ? 4 : nl <= 24 ? 5 : 6;
@@ -124,7 +130,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     dsum = FM(T, ad, dsum);
                     wsum = FM(T, alpha, wsum);
                     T = test_T;
-                    last_in_batch = c0 + b;
+                    last_in_batch = c31 - p;
                     if (STATS) st_blended++;
                 }
             }
