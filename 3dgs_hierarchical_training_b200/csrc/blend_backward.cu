@@ -306,8 +306,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 // any live lane is rare (3 % at config 3), and the branch around an 18-instruction block cost a
                 // BSSY/BRA/BSYNC triple plus the zero defaults in every visit.
                 const float2 q2 = lds64(a + 32);  // b, depth
-                // T = T / (1 - alpha), backward.cu:534.  One Newton step on the hardware reciprocal
-                // (<= 1 ulp from div.rn, 4 issue slots instead of 10); also feeds the background term.
+                // T = T / (1 - alpha), backward.cu:534.  One Newton step on the hardware reciprocal (<= 1 ulp from div.rn, 4
+                // issue slots instead of 10); also feeds the background term.  Without the Newton step (2 instructions
+                // fewer) the error of T compounds along the blend chain and dL_dcov3D misses the element-wise bar at
+                // config 5 (excess 1.04).
                 const float one_m_a = SB(1.f, alpha);
                 float rinv;
                 asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(one_m_a));
@@ -316,9 +318,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 // Cd = r*d0 + g*d1 + b*d2 + depth*dd as two packed chains (da: see A)
                 float c_lo, c_hi;
                 up2(fma2(pk2(q2.x, q2.y), d2_dd, mul2(pk2(q1.z, q1.w), d0_d1)), c_lo, c_hi);
-                const float Cd = c_lo + c_hi;
-                float dL_dopa = (Cd - A) * Tn;
-                const float An = fmaf(alpha, Cd, one_m_a * A);
+                const float D = (c_lo + c_hi) - A;          // Cd - A
+                float dL_dopa = D * Tn;
+                const float An = fmaf(alpha, D, A);         // alpha Cd + (1 - alpha) A
                 if (warp_has_bg) dL_dopa = fmaf(bg_k, rinv, dL_dopa);
                 const float w = live ? G * dL_dopa : 0.f;
                 const float aT = live ? alpha * Tn : 0.f;
