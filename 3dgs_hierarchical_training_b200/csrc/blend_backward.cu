@@ -9,9 +9,10 @@
 //     gradients need beyond those is a per-PIXEL constant:
 //        dL/dcolour_c, dL/ddepth   = sum_pix aT * (dL/dpixel_c | dL/ddepth_pix)
 //        dL/dopacity, dL/dmean2D, dL/dconic  follow from the six moments  sum_pix w * {1, x, y, x^2, xy, y^2}
-//     with (x, y) the pixel's position relative to the tile centre; the moments about the Gaussian's centre that the
-//     reference's formulas use (backward.cu:582-598) are recovered from them once per (tile, Gaussian) when the batch is
-//     flushed (dx = X - x with X the centre's offset from the tile centre: plain polynomial expansion).
+//     with (x, y) the pixel's position relative to the centre of the warp's 8x4 block; the moments about the Gaussian's
+//     centre that the reference's formulas use (backward.cu:582-598) are recovered from them in the epilogue of every
+//     tensor-core phase (dx = X - x with X the centre's offset from the block centre: plain polynomial expansion, done
+//     while |X| is a few pixels -- one frame for the whole tile cost sub-pixel Gaussians four digits of dL/dconic).
 //  2. So the sum over a warp's 32 pixels for 8 Gaussians at a time is a small matrix product
 //        C[16 x 8] = A[16 x 64] * B[64 x 8],   A = per-pixel constants (6 monomial rows, 4 upstream-gradient rows),
 //                                              B = the (w | aT) values of 32 pixels x 8 Gaussians,
@@ -22,9 +23,9 @@
 //     monomials are small integers and exact): relative error ~2^-21 per term, far inside the 1e-4 gradient bar.
 //     r01 used a 12-shuffle / 22-select transpose-reduce per visit (~55 of 118 instructions per visit; ncu showed the
 //     ALU pipe, not FMA, as the busiest); this form needs ~16.
-//  3. The 8 warps of the tile add their 16x8 results into one per-batch shared-memory accumulator row per Gaussian
-//     (shared-memory atomics: 4 per lane per 8 visits), which the flush converts and sends to HBM as three
-//     red.global.add.v4.f32 per (tile, Gaussian).
+//  3. The 8 warps of the tile add their results (moments already about the Gaussian's centre) into one per-batch
+//     shared-memory accumulator row per Gaussian (shared-memory atomics: 4 per lane per 8 visits), which the flush
+//     scales by the per-Gaussian constants and sends to HBM as three red.global.add.v4.f32 per (tile, Gaussian).
 //
 // Per-pixel arithmetic follows the reference (same thresholds, same alpha, same T = T/(1-alpha) recurrence); only
 // the summation order / association of the gradient sums differs.  The 8x4 reach masks of blend_common.cuh skip
@@ -40,7 +41,7 @@ namespace htgs {
 constexpr int BWD_BATCH = 128;   // staged Gaussians per batch (96 / 112 / 64 measured slower in r01)
 constexpr int PH_N = 8;          // Gaussians per tensor-core phase (the N of m16n8k8)
 constexpr int PH_STRIDE = 36;    // floats per panel row: 32 pixels + 4 pad => conflict-free STS.32 by lane and LDS.128 by fragment
-constexpr int ACC_STRIDE = 12;   // per-Gaussian tile sums: [0..5] moments 1,x,y,xx,xy,yy  [6..9] colour r,g,b + depth  [10..11] pad
+constexpr int ACC_STRIDE = 12;   // per-Gaussian tile sums: [0..5] moments of w about the Gaussian's centre (1, -dx, -dy, dx dx, dx dy, dy dy)  [6..9] colour r,g,b + depth  [10..11] pad
 
 // Per-warp shared memory of the reduction.
 //   park[r][lane]   r = 0..7: w of visit r, r = 8..15: aT of visit r - 8; column = lane = pixel index inside the warp's
@@ -50,7 +51,7 @@ constexpr int ACC_STRIDE = 12;   // per-Gaussian tile sums: [0..5] moments 1,x,y
 //                   l = g*4 + t) = (A[g][k0], A[g+8][k0], A[g][k1], A[g+8][k1]) for the two pixels k0 = t*8 + 2ks,
 //                   k1 = k0 + 1 the lane covers in that k-step, so a single LDS.128 lands in the four consecutive
 //                   registers HMMA wants.  Rows of A:
-//                     0..5   monomials 1, x, y, xx, xy, yy of the pixel's tile position (small integers, exact in TF32)
+//                     0..5   monomials 1, x, y, xx, xy, yy of the pixel's position in the block (half-integers, exact in TF32)
 //                     6, 7   zero
 //                     8..11  TF32 high parts of dL/dpixel r, g, b and dL/ddepth
 //                     12..15 the low parts (d - hi) of the same four
@@ -62,8 +63,10 @@ struct __align__(16) WarpPhase {
     float4 afrag[PH_KSTEPS][32];           // 2048 B
 };
 constexpr uint32_t PH_OFF_AFRAG = PH_PARK_ROWS * PH_STRIDE * 4;
+constexpr uint32_t PH_OFF_CENTRE = 15 * PH_STRIDE * 4 + 32 * 4;  // park[15][32..33] (pad words): the block centre in pixel coordinates
 
 __device__ __forceinline__ void sts32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts64(uint32_t a, float x, float y) { asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(a), "f"(x), "f"(y) : "memory"); }
 __device__ __forceinline__ void sts32u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
 // D += A * B, m16n8k8, A row-major 16x8 (a0: row g, col t | a1: row g+8, col t | a2: row g, col t+4 | a3: row g+8, col t+4),
@@ -96,7 +99,7 @@ __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) 
 // One tensor-core phase of a warp: sums the parked (w, aT) of `cnt` <= 8 visits over the warp's 32 pixels against the
 // per-pixel constants and adds the 10 x cnt results into the batch accumulator rows.  ph = shared address of the
 // warp's WarpPhase, acc = shared address of s_acc.  Warp-collective (all 32 lanes, converged).
-__device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, int cnt, int lane, uint64_t slots) {
+__device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, uint32_t sg, int cnt, int lane, uint64_t slots) {
     __syncwarp();
     const int g = lane >> 2, t = lane & 3;
     const uint32_t aw = ph + (uint32_t)g * (PH_STRIDE * 4u) + (uint32_t)t * 32u;   // visit g, pixels t*8 .. t*8+7
@@ -129,14 +132,48 @@ __device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, int cnt,
         }
     }
     // lane (g, t) holds rows g and g+8 of columns (visits) 2t and 2t+1
-    const float x0 = cw1[0] + cw2[0], x1 = cw1[1] + cw2[1];   // moment g            (g < 6)
+    float x0 = cw1[0] + cw2[0], x1 = cw1[1] + cw2[1];         // moment g about the warp's BLOCK centre (g < 6)
     float y0 = ca1[2] + ca2[2], y1 = ca1[3] + ca2[3];         // colour/depth row g+8: high-part rows for g < 4, low-part rows above
     y0 += __shfl_xor_sync(0xffffffffu, y0, 16);               // lane g+4 holds the low-part row of the same quantity
     y1 += __shfl_xor_sync(0xffffffffu, y1, 16);
     // batch index of the Gaussian behind each visit: one byte per visit, the latest visit in the lowest byte
     const bool v0 = 2 * t < cnt, v1 = 2 * t + 1 < cnt;
-    const uint32_t s0 = (uint32_t)(slots >> (8 * ((cnt - 1 - 2 * t) & 7))) & 0xffu;
-    const uint32_t s1 = (uint32_t)(slots >> (8 * ((cnt - 2 - 2 * t) & 7))) & 0xffu;
+    // (one byte permute picks both: byte (cnt-1-2t) & 7 of the 64-bit queue into byte 0, its predecessor into byte 1)
+    const uint32_t i0 = (uint32_t)(cnt - 1 - 2 * t) & 7u, i1 = (i0 - 1u) & 7u;
+    const uint32_t both = __byte_perm((uint32_t)slots, (uint32_t)(slots >> 32), i0 | (i1 << 4));
+    const uint32_t s0 = both & 0xffu, s1 = (both >> 8) & 0xffu;
+    // Moments about the block centre -> moments about each Gaussian's own centre (d = mean - pixel, the quantities
+    // backward.cu:582-598 sums), BEFORE they meet the other warps' sums: with X = mean - block centre
+    //    sum w dx = X S0 - Sx,   sum w dx dx = X (X S0 - 2 Sx) + Sxx,   sum w dx dy = X (Y S0 - Sy) - Y Sx + Sxy,  ...
+    // The cancellation in these differences grows with (X / sigma)^2; X is a few pixels here, where one frame for the
+    // whole tile (round 2's first form: |X| up to 8 and more) cost sub-pixel Gaussians near a tile corner four digits of
+    // their conic gradient (tools/grad_margin.py).  Rows 0..2 of both visits travel through the (now free) w panel.
+    __syncwarp();
+    if (g < 3) sts64(ph + (uint32_t)g * (PH_STRIDE * 4u) + (uint32_t)t * 8u, x0, x1);
+    __syncwarp();
+    const float2 S0 = lds64(ph + (uint32_t)t * 8u), Sx = lds64(ph + PH_STRIDE * 4u + (uint32_t)t * 8u),
+                 Sy = lds64(ph + 2u * PH_STRIDE * 4u + (uint32_t)t * 8u);
+    const float2 bc = lds64(ph + PH_OFF_CENTRE);                      // block centre in pixel coordinates
+    const float2 m0 = lds64(sg + s0 * STAGED_BYTES), m1 = lds64(sg + s1 * STAGED_BYTES);   // the two Gaussians' means
+    // per-row form  r = own + A * (V * S0 - K * SK) - R * Y * Sx  (first moments are kept with the opposite sign,
+    // sum w (pixel - mean); the flush flips it back):
+    //   g:     0      1      2      3        4        5
+    //   A      -      X      Y      X        X        Y
+    //   V      0     -1     -1      X        Y        Y
+    //   K,SK   0      0      0      2,Sx     1,Sy     2,Sy
+    //   R      0      0      0      0        1        0
+    const bool usesX = g == 1 || g == 3 || g == 4, first = g < 3, cross = g == 4, kx = g == 3;
+    const float vc = g == 0 ? 0.f : -1.f, fK = g < 3 ? 0.f : (g == 4 ? 1.f : 2.f), fR = g == 4 ? 1.f : 0.f;
+    {
+        const float X = m0.x - bc.x, Y = m0.y - bc.y;
+        const float A = usesX ? X : Y, V0 = cross ? Y : A, V = first ? vc : V0;
+        x0 = fmaf(-fR, Y * Sx.x, fmaf(A, fmaf(V, S0.x, -fK * (kx ? Sx.x : Sy.x)), x0));
+    }
+    {
+        const float X = m1.x - bc.x, Y = m1.y - bc.y;
+        const float A = usesX ? X : Y, V0 = cross ? Y : A, V = first ? vc : V0;
+        x1 = fmaf(-fR, Y * Sx.y, fmaf(A, fmaf(V, S0.y, -fK * (kx ? Sx.y : Sy.y)), x1));
+    }
     float* accp = reinterpret_cast<float*>(__cvta_shared_to_generic((size_t)acc));
     if (g < 6) {
         if (v0 && x0 != 0.f) atomicAdd(accp + s0 * ACC_STRIDE + g, x0);
@@ -208,10 +245,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     // fragment lanes g*4 + (p >> 3) for every row pair (g, g+8), element (p & 1) of the k-step's pixel pair.
     const uint32_t ph = smem_u32(&s_ph[warp]);
     {
-        // pixel position relative to the tile CENTRE (half-integers in [-7.5, 7.5]; squares <= 56.25: exact in TF32).
-        // Centring keeps the offset X of a Gaussian that matters to this tile small, which bounds the cancellation in
-        // the moment shift of the flush (X^2 S0 - 2 X Sx + Sxx) by ~(X / sigma)^2 <= a few hundred.
-        const float fx = (float)lx - 7.5f, fy = (float)ly - 7.5f;
+        // pixel position relative to the centre of the warp's 8x4 BLOCK (half-integers in [-3.5, 3.5] x [-1.5, 1.5];
+        // squares <= 12.25: exact in TF32).  The phase epilogue moves the moments from there to each Gaussian's centre.
+        const float fx = (float)(lane & 7) - 3.5f, fy = (float)(lane >> 3) - 1.5f;
+        if (lane == 0) sts64(ph + PH_OFF_CENTRE, pxf + 3.5f, pyf + 1.5f);  // lane 0 is the block's top-left pixel
         const float lo_row[8] = {1.f, fx, fy, fx * fx, fx * fy, fy * fy, 0.f, 0.f};  // A rows 0..7
         float hi_row[8];                                                               // A rows 8..15
         const float dv[4] = {d0, d1, d2, dd};
@@ -332,28 +369,24 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     slots = (slots << 8) | (uint64_t)(uint32_t)(c31 - p);
                     park_at += (uint32_t)(PH_STRIDE * 4);
                     if (++parked == PH_N) {
-                        reduce_phase(ph, acc_base, PH_N, lane, slots);
+                        reduce_phase(ph, acc_base, sg_base, PH_N, lane, slots);
                         parked = 0;
                         park_at = park;
                     }
                 }
             }
         }
-        if (parked) reduce_phase(ph, acc_base, parked, lane, slots);
+        if (parked) reduce_phase(ph, acc_base, sg_base, parked, lane, slots);
         __syncthreads();
         if (tid < cnt) {
             const float4* a4 = reinterpret_cast<const float4*>(&s_acc[tid][0]);
             const float4 m0 = a4[0], m1 = a4[1], m2 = a4[2];
-            const float S0 = m0.x, Sx = m0.y, Sy = m0.z, Sxx = m0.w, Sxy = m1.x, Syy = m1.y;
+            // moments about the Gaussian's own centre, d = mean - pixel (the phase epilogues delivered them in that frame,
+            // the two first moments with the opposite sign)
+            const float S0 = m0.x, s1 = -m0.y, s2 = -m0.z, s4 = m0.w, s5 = m1.x, s6 = m1.y;
             const float gr = m1.z, gg = m1.w, gb = m2.x, gdepth = m2.y;
             const float4 q0 = s_g[tid].q0;
             const float4 q1 = s_g[tid].q1;
-            // moments about the Gaussian's centre from the moments about the tile centre: d = (X - x, Y - y)
-            const float X = q0.x - ((float)tile_x0 + 7.5f), Y = q0.y - ((float)tile_y0 + 7.5f);
-            const float s1 = fmaf(X, S0, -Sx), s2 = fmaf(Y, S0, -Sy);           // sum w dx, sum w dy
-            const float s4 = fmaf(X, s1 - Sx, Sxx);                             // sum w dx dx
-            const float s5 = fmaf(X, s2, fmaf(-Y, Sx, Sxy));                    // sum w dx dy
-            const float s6 = fmaf(Y, s2 - Sy, Syy);                             // sum w dy dy
             // moments -> gradients (backward.cu:582-598), per-Gaussian constants applied once here
             const float cy = q0.z, cz = q0.w, cx = q1.x, op = q1.y;
             const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:490-491
@@ -361,9 +394,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const float gmy = -op * (cz * s2 + cy * s1) * ddely_dy;
             const float gcx = -0.5f * op * s4, gcy = -0.5f * op * s5, gcw = -0.5f * op * s6;
             float4* dst = reinterpret_cast<float4*>(gacc + (size_t)s_id[tid] * 12);
-            if (S0 != 0.f || Sx != 0.f || Sy != 0.f || gdepth != 0.f) atomicAdd(dst, make_float4(gmx, gmy, S0, gdepth));
-            if (S0 != 0.f || Sx != 0.f || Sy != 0.f || Sxx != 0.f || Sxy != 0.f || Syy != 0.f)
-                atomicAdd(dst + 1, make_float4(gcx, gcy, gcw, 0.f));
+            if (S0 != 0.f || s1 != 0.f || s2 != 0.f || gdepth != 0.f) atomicAdd(dst, make_float4(gmx, gmy, S0, gdepth));
+            if (s4 != 0.f || s5 != 0.f || s6 != 0.f) atomicAdd(dst + 1, make_float4(gcx, gcy, gcw, 0.f));
             if (gr != 0.f || gg != 0.f || gb != 0.f) atomicAdd(dst + 2, make_float4(gr, gg, gb, 0.f));
         }
     }

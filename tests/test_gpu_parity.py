@@ -129,6 +129,28 @@ def test_cuda_matches_reference_cuda_bit_exact(cfgname, deg, precomp, use_cov, m
     refcuda.dgr().ref_release()  # give the reference's geometry / binning / image buffers back (6M Gaussians: ~1.5 GB)
 
 
+# Gradients against the live reference CUDA under other backgrounds than the one above.  Found with tools/grad_margin.py:
+# with background (0.1, 0.2, 0.3) at config 5 the first tensor-core form of the backward (moments about the TILE centre,
+# shifted to the Gaussian's centre when the batch is flushed) left dL_dcov3D of a sub-pixel Gaussian near a tile corner
+# at 1.35-1.7x the element-wise bar while every committed case passed.  Since the shift happens per warp from its 8x4
+# block's centre, all tensors sit at <= 0.16 of the bar and <= 3e-6 of each tensor's largest entry on configs 2 / 3 / 5;
+# the assertions below hold them to a quarter of the bar and to 1e-5.
+@pytest.mark.skipif(not refcuda.available(), reason="oracle/_ref (reference CUDA build) did not travel to this box")
+@pytest.mark.parametrize("cfgname,bgv", [("config5", (0.1, 0.2, 0.3)), ("config5", (0.0, 0.0, 0.0)), ("config3", (0.1, 0.2, 0.3)),
+                                         ("config2", (1.0, 1.0, 1.0))])
+def test_gradients_vs_reference_cuda_other_backgrounds(cfgname, bgv):
+    cfg, scene, cam, up, bg, colors, cov, kw = _case(cfgname, 3, bgv=bgv)
+    mine = run_ours(scene, cam, up, bg, 3)
+    r = refcuda.forward(scene["means3D"], scene["opacities"], cam, bg, 3, **kw)
+    rg = refcuda.backward(r, scene["means3D"], cam, bg, up["dL_dcolor"], up["dL_ddepth"], up["dL_dalpha"], 3, **kw)
+    torch.cuda.synchronize()
+    assert bits_equal(mine["color"], r["color"])
+    for k in _grad_list(False, False):
+        assert rel_inf(mine["grads"][k], rg[k].view(mine["grads"][k].shape)) <= 1e-5, k
+        assert elem_excess(mine["grads"][k], rg[k].view(mine["grads"][k].shape)) <= 0.25, k
+    refcuda.dgr().ref_release()
+
+
 REFCUDA_CASES = [p for p in sorted(glob.glob(os.path.join(GOLD, "refcuda_*.npz"))) if not p.endswith("refcuda_knn.npz")]
 
 
