@@ -95,6 +95,16 @@ __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) 
     hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
     lo = __float_as_uint(x - __uint_as_float(hi));
 }
+// The B operand (parked w / aT, 16 values per lane and phase) is split by TRUNCATION instead: the tensor core ignores the
+// 13 low mantissa bits of a TF32 input, so x itself serves as its own high part at no cost, and the low part is
+// x - (x with those bits cleared) -- one LOP3 and half a packed FADD2 per value instead of three instructions.  |lo| is
+// below 2^-10 |x| (2^-11 when rounding), so what the tensor core drops of lo is below 2^-20 |x| per element.
+__device__ __forceinline__ void split_tf32_pair(float x0, float x1, uint32_t& lo0, uint32_t& lo1) {
+    float l0, l1;
+    up2(sub2(pk2(x0, x1), pk2(__uint_as_float(__float_as_uint(x0) & 0xffffe000u), __uint_as_float(__float_as_uint(x1) & 0xffffe000u))), l0, l1);
+    lo0 = __float_as_uint(l0);
+    lo1 = __float_as_uint(l1);
+}
 
 // One tensor-core phase of a warp: sums the parked (w, aT) of `cnt` <= 8 visits over the warp's 32 pixels against the
 // per-pixel constants and adds the 10 x cnt results into the batch accumulator rows.  ph = shared address of the
@@ -105,6 +115,16 @@ __device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, uint32_t
     const uint32_t aw = ph + (uint32_t)g * (PH_STRIDE * 4u) + (uint32_t)t * 32u;   // visit g, pixels t*8 .. t*8+7
     const uint32_t aa = aw + (uint32_t)PH_ROW_AT * (PH_STRIDE * 4u);
     const uint32_t af = ph + PH_OFF_AFRAG + (uint32_t)lane * 16u;
+    // batch index of the Gaussian behind each of this lane's two visits: one byte per visit, the latest visit in the lowest
+    // byte (one byte permute picks both: byte (cnt-1-2t) & 7 of the 64-bit queue into byte 0, its predecessor into byte 1)
+    const bool v0 = 2 * t < cnt, v1 = 2 * t + 1 < cnt;
+    const uint32_t i0 = (uint32_t)(cnt - 1 - 2 * t) & 7u, i1 = (i0 - 1u) & 7u;
+    const uint32_t both = __byte_perm((uint32_t)slots, (uint32_t)(slots >> 32), i0 | (i1 << 4));
+    const uint32_t s0 = both & 0xffu, s1 = (both >> 8) & 0xffu;
+    // the two Gaussians' centres relative to the block centre -- loaded here so that the loads complete under the MMAs (the
+    // phase is a chain of dependent latencies, not of issue slots)
+    const float2 bc = lds64(ph + PH_OFF_CENTRE), m0 = lds64(sg + s0 * STAGED_BYTES), m1 = lds64(sg + s1 * STAGED_BYTES);
+    const float X0 = m0.x - bc.x, Y0 = m0.y - bc.y, X1 = m1.x - bc.x, Y1 = m1.y - bc.y;
     float cw1[4], cw2[4], ca1[4], ca2[4];  // four independent chains: (w_hi, w_lo, aT_hi, aT_lo) against the same A
 #pragma unroll
     for (int half = 0; half < 2; half++) {
@@ -113,11 +133,11 @@ __device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, uint32_t
 #pragma unroll
         for (int k = 0; k < 2; k++) {  // k-step 2*half + k: elements 2k (k-index t) and 2k+1 (k-index t+4)
             const float4 a = lds128(af + (uint32_t)(2 * half + k) * (32u * 16u));
-            uint32_t wh0, wl0, wh1, wl1, th0, tl0, th1, tl1;
-            split_tf32(wv[2 * k], wh0, wl0);
-            split_tf32(wv[2 * k + 1], wh1, wl1);
-            split_tf32(tv[2 * k], th0, tl0);
-            split_tf32(tv[2 * k + 1], th1, tl1);
+            uint32_t wl0, wl1, tl0, tl1;
+            const uint32_t wh0 = __float_as_uint(wv[2 * k]), wh1 = __float_as_uint(wv[2 * k + 1]);
+            const uint32_t th0 = __float_as_uint(tv[2 * k]), th1 = __float_as_uint(tv[2 * k + 1]);
+            split_tf32_pair(wv[2 * k], wv[2 * k + 1], wl0, wl1);
+            split_tf32_pair(tv[2 * k], tv[2 * k + 1], tl0, tl1);
             if (half == 0 && k == 0) {
                 mma_tf32_first(cw1, a, wh0, wh1);
                 mma_tf32_first(cw2, a, wl0, wl1);
@@ -136,25 +156,19 @@ __device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, uint32_t
     float y0 = ca1[2] + ca2[2], y1 = ca1[3] + ca2[3];         // colour/depth row g+8: high-part rows for g < 4, low-part rows above
     y0 += __shfl_xor_sync(0xffffffffu, y0, 16);               // lane g+4 holds the low-part row of the same quantity
     y1 += __shfl_xor_sync(0xffffffffu, y1, 16);
-    // batch index of the Gaussian behind each visit: one byte per visit, the latest visit in the lowest byte
-    const bool v0 = 2 * t < cnt, v1 = 2 * t + 1 < cnt;
-    // (one byte permute picks both: byte (cnt-1-2t) & 7 of the 64-bit queue into byte 0, its predecessor into byte 1)
-    const uint32_t i0 = (uint32_t)(cnt - 1 - 2 * t) & 7u, i1 = (i0 - 1u) & 7u;
-    const uint32_t both = __byte_perm((uint32_t)slots, (uint32_t)(slots >> 32), i0 | (i1 << 4));
-    const uint32_t s0 = both & 0xffu, s1 = (both >> 8) & 0xffu;
     // Moments about the block centre -> moments about each Gaussian's own centre (d = mean - pixel, the quantities
     // backward.cu:582-598 sums), BEFORE they meet the other warps' sums: with X = mean - block centre
     //    sum w dx = X S0 - Sx,   sum w dx dx = X (X S0 - 2 Sx) + Sxx,   sum w dx dy = X (Y S0 - Sy) - Y Sx + Sxy,  ...
     // The cancellation in these differences grows with (X / sigma)^2; X is a few pixels here, where one frame for the
     // whole tile (round 2's first form: |X| up to 8 and more) cost sub-pixel Gaussians near a tile corner four digits of
-    // their conic gradient (tools/grad_margin.py).  Rows 0..2 of both visits travel through the (now free) w panel.
-    __syncwarp();
-    if (g < 3) sts64(ph + (uint32_t)g * (PH_STRIDE * 4u) + (uint32_t)t * 8u, x0, x1);
-    __syncwarp();
-    const float2 S0 = lds64(ph + (uint32_t)t * 8u), Sx = lds64(ph + PH_STRIDE * 4u + (uint32_t)t * 8u),
-                 Sy = lds64(ph + 2u * PH_STRIDE * 4u + (uint32_t)t * 8u);
-    const float2 bc = lds64(ph + PH_OFF_CENTRE);                      // block centre in pixel coordinates
-    const float2 m0 = lds64(sg + s0 * STAGED_BYTES), m1 = lds64(sg + s1 * STAGED_BYTES);   // the two Gaussians' means
+    // their conic gradient (tools/grad_margin.py).
+    float2 S0, Sx, Sy;  // rows 0..2 of this lane's two visits: held by lanes t, 4 + t, 8 + t
+    S0.x = __shfl_sync(0xffffffffu, x0, t);
+    S0.y = __shfl_sync(0xffffffffu, x1, t);
+    Sx.x = __shfl_sync(0xffffffffu, x0, 4 + t);
+    Sx.y = __shfl_sync(0xffffffffu, x1, 4 + t);
+    Sy.x = __shfl_sync(0xffffffffu, x0, 8 + t);
+    Sy.y = __shfl_sync(0xffffffffu, x1, 8 + t);
     // per-row form  r = own + A * (V * S0 - K * SK) - R * Y * Sx  (first moments are kept with the opposite sign,
     // sum w (pixel - mean); the flush flips it back):
     //   g:     0      1      2      3        4        5
@@ -165,14 +179,12 @@ __device__ __forceinline__ void reduce_phase(uint32_t ph, uint32_t acc, uint32_t
     const bool usesX = g == 1 || g == 3 || g == 4, first = g < 3, cross = g == 4, kx = g == 3;
     const float vc = g == 0 ? 0.f : -1.f, fK = g < 3 ? 0.f : (g == 4 ? 1.f : 2.f), fR = g == 4 ? 1.f : 0.f;
     {
-        const float X = m0.x - bc.x, Y = m0.y - bc.y;
-        const float A = usesX ? X : Y, V0 = cross ? Y : A, V = first ? vc : V0;
-        x0 = fmaf(-fR, Y * Sx.x, fmaf(A, fmaf(V, S0.x, -fK * (kx ? Sx.x : Sy.x)), x0));
+        const float A = usesX ? X0 : Y0, V0 = cross ? Y0 : A, V = first ? vc : V0;
+        x0 = fmaf(-fR, Y0 * Sx.x, fmaf(A, fmaf(V, S0.x, -fK * (kx ? Sx.x : Sy.x)), x0));
     }
     {
-        const float X = m1.x - bc.x, Y = m1.y - bc.y;
-        const float A = usesX ? X : Y, V0 = cross ? Y : A, V = first ? vc : V0;
-        x1 = fmaf(-fR, Y * Sx.y, fmaf(A, fmaf(V, S0.y, -fK * (kx ? Sx.y : Sy.y)), x1));
+        const float A = usesX ? X1 : Y1, V0 = cross ? Y1 : A, V = first ? vc : V0;
+        x1 = fmaf(-fR, Y1 * Sx.y, fmaf(A, fmaf(V, S0.y, -fK * (kx ? Sx.y : Sy.y)), x1));
     }
     float* accp = reinterpret_cast<float*>(__cvta_shared_to_generic((size_t)acc));
     if (g < 6) {
