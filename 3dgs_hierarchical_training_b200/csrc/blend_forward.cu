@@ -116,9 +116,14 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 #pragma unroll
                     for (int k = 0; k < 7; k++) st_hist[k] += (k == bucket) ? 1u : 0u;
                 }
-                const bool blend = live && !(test_T < 0.0001f);
-                if (kill) T = -fabsf(T);
-                if (blend) {
+                // skip = !live || test_T < 1e-4 serves both the saturation mark (live && skip) and the blend (!skip); written in
+                // PTX because nvcc otherwise derives a second comparison (test_T >= 1e-4) for the mark
+                int skip_i;
+                asm("{\n\t.reg .pred l, s;\n\t.reg .f32 t;\n\tsetp.ne.b32 l, %3, 0;\n\tsetp.lt.or.f32 s, %2, 0f38D1B717, !l;\n\t"
+                    "abs.f32 t, %0;\n\tneg.f32 t, t;\n\t@l selp.f32 %0, t, %0, s;\n\tselp.u32 %1, 1, 0, s;\n\t}"
+                    : "+f"(T), "=r"(skip_i) : "f"(test_T), "r"((int)live));
+                const bool skip = skip_i != 0;
+                if (!skip) {
                     const float2 q2 = lds64(a + 32);  // b, depth
                     const uint64_t aa = pk2(alpha, alpha);
                     float ac0, ac1, ac2, ad;
